@@ -1,0 +1,195 @@
+"""ctypes/numpy front end of the CPU oracle (oracle/sdm_oracle.c).
+
+TEST INFRASTRUCTURE, NOT PRODUCT CODE: may be imported only by tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+Function names and argument order follow the reference's Numba backend methods
+(/root/reference/PySDM/backends/impl_numba/methods/*.py; each C function cites
+its file:line), operating in place on numpy arrays.
+"""
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libsdm_oracle.so")
+
+i64 = ctypes.c_int64
+f64 = ctypes.c_double
+ptr = ctypes.c_void_p
+
+
+def build(force=False):
+    """compile the C restatement with the system gcc (seconds)"""
+    src = os.path.join(_HERE, "sdm_oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib  # pylint: disable=global-statement
+    if _lib is None:
+        build()
+        _lib = ctypes.CDLL(_SO)
+        _lib.oracle_remove_zero_n_or_flagged.restype = i64
+        _lib.oracle_adaptive_sdm_end.restype = i64
+        _lib.oracle_collision_coalescence_breakup.restype = i64
+    return _lib
+
+
+def _p(a, dtype=None):
+    """pointer to a C-contiguous numpy array (checked, never copied)"""
+    assert isinstance(a, np.ndarray), type(a)
+    assert a.flags["C_CONTIGUOUS"]
+    if dtype is not None:
+        assert a.dtype == dtype, (a.dtype, dtype)
+    return ptr(a.ctypes.data)
+
+
+def _pi(a):
+    return _p(a, np.int64)
+
+
+def _pf(a):
+    return _p(a, np.float64)
+
+
+def _pb(a):
+    assert a.dtype in (np.bool_, np.uint8)
+    return _p(a)
+
+
+# ---- index methods -----------------------------------------------------------
+def pair_indices(idx, is_first_in_pair, prob_like):
+    n = len(prob_like)
+    j = np.empty(n, np.int64)
+    k = np.empty(n, np.int64)
+    skip = np.empty(n, np.uint8)
+    lib().oracle_pair_indices(i64(n), _pi(idx), _pb(is_first_in_pair), _pf(prob_like),
+                              _pi(j), _pi(k), _pb(skip))
+    return j, k, skip.astype(bool)
+
+
+def identity_index(idx):
+    lib().oracle_identity_index(_pi(idx), i64(len(idx)))
+
+
+def shuffle_global(idx, length, u01):
+    lib().oracle_shuffle_global(_pi(idx), i64(length), _pf(u01))
+
+
+def shuffle_local(idx, u01, cell_start):
+    lib().oracle_shuffle_local(_pi(idx), _pf(u01), _pi(cell_start), i64(len(cell_start) - 1))
+
+
+def sort_by_key(idx, attr):
+    lib().oracle_sort_by_key(_pi(idx), _pf(attr), i64(len(attr)))
+
+
+def remove_zero_n_or_flagged(multiplicity, idx, length):
+    return int(lib().oracle_remove_zero_n_or_flagged(_pi(multiplicity), _pi(idx), i64(length),
+                                                     i64(len(idx))))
+
+
+def counting_sort_by_cell_id(new_idx, idx, cell_id, cell_idx, length, cell_start):
+    lib().oracle_counting_sort_by_cell_id(_pi(new_idx), _pi(idx), _pi(cell_id), _pi(cell_idx),
+                                          i64(length), _pi(cell_start), i64(len(cell_start)))
+
+
+def cell_id(cell_id_out, cell_origin, strides):
+    n_dims, n_sd = cell_origin.shape
+    strides = np.ascontiguousarray(np.asarray(strides, dtype=np.int64).ravel())
+    lib().oracle_cell_id(_pi(cell_id_out), _pi(cell_origin), _pi(strides), i64(n_dims), i64(n_sd))
+
+
+# ---- pair methods --------------------------------------------------------------
+def find_pairs(cell_start, is_first_in_pair, cell_id_, cell_idx, idx, length):
+    lib().oracle_find_pairs(_pi(cell_start), _pb(is_first_in_pair), _pi(cell_id_), _pi(cell_idx),
+                            _pi(idx), i64(length))
+
+
+def sort_within_pair_by_attr(idx, length, is_first_in_pair, attr):
+    if attr.dtype == np.int64:
+        lib().oracle_sort_within_pair_by_attr_i64(_pi(idx), i64(length), _pb(is_first_in_pair),
+                                                  _pi(attr))
+    else:
+        lib().oracle_sort_within_pair_by_attr_f64(_pi(idx), i64(length), _pb(is_first_in_pair),
+                                                  _pf(attr))
+
+
+PAIR_OPS = {"distance": 0, "max": 1, "min": 2, "sum": 3, "multiply": 4}
+
+
+def pair_op(op, data_out, data_in, is_first_in_pair, idx, length):
+    fun = lib().oracle_pair_op_i64 if data_in.dtype == np.int64 else lib().oracle_pair_op_f64
+    fun(ctypes.c_int(PAIR_OPS[op]), _pf(data_out), i64(len(data_out)), _p(data_in),
+        _pb(is_first_in_pair), _pi(idx), i64(length))
+
+
+def sort_pair(data_out, data_in, is_first_in_pair, idx, length):
+    lib().oracle_sort_pair_f64(_pf(data_out), i64(len(data_out)), _pf(data_in),
+                               _pb(is_first_in_pair), _pi(idx), i64(length))
+
+
+# ---- physics ---------------------------------------------------------------------
+def volume_of_water_mass(volume, mass, rho_w):
+    lib().oracle_volume_of_water_mass(_pf(volume), _pf(mass), i64(len(volume)), f64(rho_w))
+
+
+def mass_of_water_volume(mass, volume, rho_w):
+    lib().oracle_mass_of_water_volume(_pf(mass), _pf(volume), i64(len(volume)), f64(rho_w))
+
+
+# ---- collisions --------------------------------------------------------------------
+def normalize(prob, cell_id_, cell_idx, cell_start, norm_factor, timestep, dv):
+    lib().oracle_normalize(_pf(prob), i64(len(prob)), _pi(cell_id_), _pi(cell_idx),
+                           _pi(cell_start), i64(len(cell_start) - 1), _pf(norm_factor),
+                           f64(timestep), f64(dv))
+
+
+def compute_gamma(prob, rand, idx, length, multiplicity, cell_id_, collision_rate_deficit,
+                  collision_rate, is_first_in_pair, out):
+    lib().oracle_compute_gamma(_pf(prob), _pf(rand), _pi(idx), i64(length), _pi(multiplicity),
+                               _pi(cell_id_), _pi(collision_rate_deficit), _pi(collision_rate),
+                               _pb(is_first_in_pair), _pf(out))
+
+
+def collision_coalescence(multiplicity, idx, length, attributes, gamma, healthy, cell_id_,
+                          coalescence_rate, is_first_in_pair):
+    n_attr, n_sd = attributes.shape
+    lib().oracle_collision_coalescence(_pi(multiplicity), _pi(idx), i64(length), _pf(attributes),
+                                       i64(n_attr), i64(n_sd), _pf(gamma), _pi(healthy),
+                                       _pi(cell_id_), _pi(coalescence_rate),
+                                       _pb(is_first_in_pair))
+
+
+def adaptive_sdm_end(dt_left, cell_start):
+    return int(lib().oracle_adaptive_sdm_end(_pf(dt_left), i64(len(dt_left)), _pi(cell_start)))
+
+
+def scale_prob_for_adaptive_sdm_gamma(prob, idx, length, multiplicity, cell_id_, dt_left, dt,
+                                      dt_range, is_first_in_pair, stats_n_substep, stats_dt_min):
+    lib().oracle_scale_prob_for_adaptive_sdm_gamma(
+        _pf(prob), _pi(idx), i64(length), _pi(multiplicity), _pi(cell_id_), _pf(dt_left),
+        i64(len(dt_left)), f64(dt), f64(dt_range[0]), f64(dt_range[1]), _pb(is_first_in_pair),
+        _pi(stats_n_substep), _pf(stats_dt_min))
+
+
+def collision_coalescence_breakup(multiplicity, idx, length, attributes, gamma, rand, Ec, Eb,
+                                  fragment_mass, healthy, cell_id_, coalescence_rate,
+                                  breakup_rate, breakup_rate_deficit, is_first_in_pair,
+                                  max_multiplicity, particle_mass, handle_all_breakups=False):
+    """returns the number of pairs that raised the overflow flag"""
+    n_attr, n_sd = attributes.shape
+    return int(lib().oracle_collision_coalescence_breakup(
+        _pi(multiplicity), _pi(idx), i64(length), _pf(attributes), i64(n_attr), i64(n_sd),
+        _pf(gamma), _pf(rand), _pf(Ec), _pf(Eb), _pf(fragment_mass), _pi(healthy), _pi(cell_id_),
+        _pi(coalescence_rate), _pi(breakup_rate), _pi(breakup_rate_deficit),
+        _pb(is_first_in_pair), f64(max_multiplicity), _pf(particle_mass),
+        ctypes.c_int(int(handle_all_breakups))))

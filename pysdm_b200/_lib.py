@@ -1,0 +1,86 @@
+"""ctypes binding of libpysdm_b200.so (the C-ABI declared in include/pysdm_b200.h).
+
+There is NO fallback: if the CUDA library is missing or no CUDA device is present the
+backend cannot be constructed and says so.
+"""
+
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libpysdm_b200.so")
+
+P = ctypes.c_void_p
+I64 = ctypes.c_int64
+U64 = ctypes.c_uint64
+U32 = ctypes.c_uint32
+F64 = ctypes.c_double
+INT = ctypes.c_int
+SIZE = ctypes.c_size_t
+
+# name -> (restype, argtypes); mirrors include/pysdm_b200.h one to one
+SIGNATURES = {
+    "pysdm_b200_identity_index": (INT, (P, I64, P)),
+    "pysdm_b200_shuffle_workspace_bytes": (SIZE, (I64,)),
+    "pysdm_b200_shuffle_global": (INT, (P, I64, P, P, SIZE, P)),
+    "pysdm_b200_shuffle_local": (INT, (P, P, P, I64, I64, P, SIZE, P)),
+    "pysdm_b200_sort_by_cell_workspace_bytes": (SIZE, (I64,)),
+    "pysdm_b200_sort_by_cell_id": (INT, (P, P, P, P, I64, P, I64, P, SIZE, P)),
+    "pysdm_b200_sort_by_key_workspace_bytes": (SIZE, (I64,)),
+    "pysdm_b200_sort_by_key": (INT, (P, P, I64, P, SIZE, P)),
+    "pysdm_b200_remove_zero_workspace_bytes": (SIZE, (I64,)),
+    "pysdm_b200_remove_zero_n_or_flagged": (INT, (P, P, I64, I64, P, P, SIZE, P)),
+    "pysdm_b200_cell_id": (INT, (P, P, P, I64, I64, P)),
+    "pysdm_b200_find_pairs": (INT, (P, P, P, P, P, I64, P)),
+    "pysdm_b200_sort_within_pair_by_attr": (INT, (P, I64, P, P, INT, P)),
+    "pysdm_b200_pair_op": (INT, (INT, P, I64, P, INT, P, P, I64, P)),
+    "pysdm_b200_sort_pair": (INT, (P, I64, P, P, P, I64, P)),
+    "pysdm_b200_normalize": (INT, (P, I64, P, P, P, I64, P, F64, F64, P)),
+    "pysdm_b200_compute_gamma": (INT, (P, P, P, I64, P, P, P, P, P, P, P)),
+    "pysdm_b200_scale_prob_for_adaptive_sdm_gamma": (
+        INT, (P, P, I64, P, P, P, I64, F64, F64, F64, P, P, P, P, P)),
+    "pysdm_b200_adaptive_sdm_end": (INT, (P, I64, P, P, P, P)),
+    "pysdm_b200_collision_coalescence": (INT, (P, P, I64, P, I64, I64, P, P, P, P, P, P)),
+    "pysdm_b200_elementwise": (INT, (INT, P, P, P, F64, I64, P)),
+    "pysdm_b200_row_modulo": (INT, (P, P, I64, I64, P)),
+    "pysdm_b200_reduce_scratch_bytes": (SIZE, ()),
+    "pysdm_b200_minmax_f64": (INT, (P, I64, INT, P, P, P)),
+    "pysdm_b200_minmax_i64": (INT, (P, I64, INT, P, P, P)),
+    "pysdm_b200_philox_uniform": (INT, (P, I64, U64, U64, P)),
+    "pysdm_b200_philox_raw": (INT, (P, U32, U32, U32, U32, U32, U32, P)),
+    "pysdm_b200_volume_of_water_mass": (INT, (P, P, I64, F64, P)),
+    "pysdm_b200_mass_of_water_volume": (INT, (P, P, I64, F64, P)),
+}
+
+EW = {"add": 0, "sub": 1, "mul": 2, "div": 3, "div_if_not_zero": 4, "pow": 5, "axpy": 6,
+      "floor": 7, "exp": 8, "abs": 9, "mod": 10}
+PAIR_OPS = {"distance": 0, "max": 1, "min": 2, "sum": 3, "multiply": 4}
+
+
+class CudaLibraryError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """loads the shared library once; raises if it has not been built"""
+    global _lib  # pylint: disable=global-statement
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise CudaLibraryError(
+                f"{SO_PATH} is missing: build it with `python -m pysdm_b200.build` "
+                "(pysdm_b200 has no CPU fallback)")
+        lib = ctypes.CDLL(SO_PATH)
+        for name, (restype, argtypes) in SIGNATURES.items():
+            fun = getattr(lib, name)
+            fun.restype = restype
+            fun.argtypes = argtypes
+        _lib = lib
+    return _lib
+
+
+def check(err, what=""):
+    if err != 0:
+        raise CudaLibraryError(f"CUDA error {err} in {what}")

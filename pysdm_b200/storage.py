@@ -1,0 +1,315 @@
+"""`Storage` of the B200 backend: a typed view of device memory (a torch CUDA tensor is
+used purely as the allocation/slicing handle) with the in-place operator set the
+reference's storage defines (PySDM/backends/impl_numba/storage.py:16-213 and
+impl_common/storage_utils.py:16-79).  Arithmetic goes through our own kernels
+(csrc/storage_ops.cu); torch is only used to allocate, slice, fill and copy.
+"""
+
+import ctypes
+from collections import namedtuple
+
+import numpy as np
+import torch
+
+from . import _lib
+
+try:  # when PySDM is importable the reference's own base classes are used (drop-in)
+    from PySDM.backends.impl_common.storage_utils import StorageBase, StorageSignature
+except ImportError:  # stand-alone: same fields, same dunder behaviour
+    class StorageSignature(namedtuple("StorageSignature", ("data", "shape", "dtype"))):
+        __slots__ = ()
+
+    class StorageBase:
+        def __init__(self, signature):
+            self.data = signature.data
+            self.shape = ((signature.shape,) if isinstance(signature.shape, (int, np.integer))
+                          else signature.shape)
+            self.dtype = signature.dtype
+            self.backend = None
+
+        def __len__(self):
+            return self.shape[0]
+
+        @staticmethod
+        def _use_inplace(symbol):
+            raise TypeError(f"Use {symbol}=")
+
+        def __pow__(self, other):
+            self._use_inplace("**")
+
+        def __mod__(self, other):
+            self._use_inplace("%")
+
+        def __truediv__(self, other):
+            self._use_inplace("/")
+
+        def __mul__(self, other):
+            self._use_inplace("*")
+
+        def __sub__(self, other):
+            self._use_inplace("-")
+
+        def __add__(self, other):
+            self._use_inplace("+")
+
+
+DEVICE = "cuda"
+_TORCH = {np.float64: torch.float64, np.int64: torch.int64, np.bool_: torch.bool}
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def ptr(tensor):
+    """raw device pointer of a contiguous tensor (or None)"""
+    if tensor is None:
+        return None
+    assert tensor.is_contiguous(), "non-contiguous device view"
+    return tensor.data_ptr()
+
+
+class _Scratch:
+    """per-process device scratch + a pinned two-word mailbox for host results"""
+
+    def __init__(self):
+        self.buffers = {}
+        self.mailbox = None
+
+    def device(self, key, nbytes):
+        buf = self.buffers.get(key)
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=DEVICE)
+            self.buffers[key] = buf
+        return buf
+
+    def host(self):
+        if self.mailbox is None:
+            self.mailbox = torch.zeros(2, dtype=torch.int64).pin_memory()
+        return self.mailbox
+
+
+SCRATCH = _Scratch()
+
+
+class Storage(StorageBase):
+    FLOAT = np.float64
+    INT = np.int64
+    BOOL = np.bool_
+
+    # ---- construction -------------------------------------------------------------
+    @staticmethod
+    def _normalize_dtype(dtype):
+        if dtype in (float, Storage.FLOAT):
+            return Storage.FLOAT
+        if dtype in (int, Storage.INT):
+            return Storage.INT
+        if dtype in (bool, Storage.BOOL):
+            return Storage.BOOL
+        raise NotImplementedError(dtype)
+
+    @staticmethod
+    def _get_empty_data(shape, dtype):
+        dtype = Storage._normalize_dtype(dtype)
+        size = (shape,) if isinstance(shape, (int, np.integer)) else tuple(shape)
+        # same initial content as the reference: NaN / -1 / True
+        fill = {Storage.FLOAT: float("nan"), Storage.INT: -1, Storage.BOOL: True}[dtype]
+        data = torch.full(size, fill, dtype=_TORCH[dtype], device=DEVICE)
+        return StorageSignature(data, shape, dtype)
+
+    @staticmethod
+    def empty(shape, dtype):
+        return Storage(Storage._get_empty_data(shape, dtype))
+
+    @staticmethod
+    def _get_data_from_ndarray(array):
+        array = np.asarray(array)
+        kind = str(array.dtype)
+        if kind.startswith("int"):
+            dtype = Storage.INT
+        elif kind.startswith("float"):
+            dtype = Storage.FLOAT
+        elif kind.startswith("bool"):
+            dtype = Storage.BOOL
+        else:
+            raise NotImplementedError(kind)
+        host = np.ascontiguousarray(array.astype(dtype))
+        data = torch.from_numpy(host).to(DEVICE)
+        return StorageSignature(data, array.shape, dtype)
+
+    @staticmethod
+    def from_ndarray(array):
+        return Storage(Storage._get_data_from_ndarray(array))
+
+    # ---- views & element access -----------------------------------------------------
+    def __getitem__(self, item):
+        dim = len(self.shape)
+        if isinstance(item, slice):
+            if (item.step or 1) != 1:
+                raise NotImplementedError("step != 1")
+            start = item.start or 0
+            if dim == 1:
+                stop = item.stop or len(self)
+                shape = (stop - start,)
+            elif dim == 2:
+                stop = item.stop or self.shape[0]
+                shape = (stop - start, self.shape[1])
+            else:
+                raise NotImplementedError("Only 2 or less dimensions array is supported.")
+            if stop > self.data.shape[0]:
+                raise IndexError(f"requested a slice ({start}:{stop}) of Storage"
+                                 f" with first dim of length {self.data.shape[0]}")
+            return Storage(StorageSignature(self.data[item], shape, self.dtype))
+        if isinstance(item, tuple) and dim == 2 and isinstance(item[1], slice):
+            return Storage(StorageSignature(self.data[item[0]], (*self.shape[1:],), self.dtype))
+        return self.data[item].item()  # host scalar (device sync)
+
+    def __setitem__(self, key, value):
+        if hasattr(value, "data") and isinstance(value.data, torch.Tensor):
+            value = value.data
+        elif isinstance(value, np.ndarray):
+            value = torch.from_numpy(np.ascontiguousarray(value)).to(DEVICE)
+        self.data[key] = value
+        return self
+
+    # ---- arithmetic (own kernels) -----------------------------------------------------
+    def _ew(self, op, a=None, b=None, scalar=0.0, out=None):
+        assert self.dtype is Storage.FLOAT, "elementwise arithmetic is defined for fp64 storages"
+        out = self.data if out is None else out
+        _lib.check(_lib.load().pysdm_b200_elementwise(
+            _lib.EW[op], ptr(out), ptr(a), ptr(b), float(scalar), out.numel(), stream()), op)
+        return self
+
+    @staticmethod
+    def _operand(other):
+        """-> (tensor or None, scalar)"""
+        if hasattr(other, "data") and isinstance(other.data, torch.Tensor):
+            return other.data, 0.0
+        if isinstance(other, torch.Tensor):
+            return other, 0.0
+        return None, float(other)
+
+    def __iadd__(self, other):
+        if (isinstance(other, tuple) and len(other) == 3 and isinstance(other[0], float)
+                and other[1] == "*" and isinstance(other[2], Storage)):
+            return self._ew("axpy", self.data, other[2].data, other[0])
+        if self.dtype is not Storage.FLOAT:
+            tensor, scalar = self._operand(other)
+            self.data += tensor if tensor is not None else int(scalar)
+            return self
+        tensor, scalar = self._operand(other)
+        return self._ew("add", self.data, tensor, scalar)
+
+    def __isub__(self, other):
+        return self._ew("sub", self.data, other.data)
+
+    def __imul__(self, other):
+        tensor, scalar = self._operand(other)
+        return self._ew("mul", self.data, tensor, scalar)
+
+    def __itruediv__(self, other):
+        tensor, scalar = self._operand(other)
+        return self._ew("div", self.data, tensor, scalar)
+
+    def __imod__(self, other):
+        n_rows, n_cols = (self.shape if len(self.shape) == 2 else (1, self.shape[0]))
+        _lib.check(_lib.load().pysdm_b200_row_modulo(ptr(self.data), ptr(other.data), n_rows,
+                                                    n_cols, stream()), "row_modulo")
+        return self
+
+    def __ipow__(self, other):
+        return self._ew("pow", self.data, None, float(other))
+
+    def floor(self, other=None):
+        return self._ew("floor", None, self.data if other is None else other.data)
+
+    def product(self, multiplicand, multiplier):
+        tensor, scalar = self._operand(multiplier)
+        return self._ew("mul", multiplicand.data, tensor, scalar)
+
+    def ratio(self, dividend, divisor):
+        return self._ew("div", dividend.data, divisor.data)
+
+    def divide_if_not_zero(self, divisor):
+        return self._ew("div_if_not_zero", self.data, divisor.data)
+
+    def sum(self, arg_a, arg_b):
+        return self._ew("add", arg_a.data, arg_b.data)
+
+    def exp(self):
+        self._ew("exp", None, self.data)
+
+    def abs(self):
+        self._ew("abs", None, self.data)
+
+    # ---- reductions (host result => device sync) ---------------------------------------
+    def _minmax(self, is_max):
+        lib = _lib.load()
+        scratch = SCRATCH.device("reduce", lib.pysdm_b200_reduce_scratch_bytes())
+        box = SCRATCH.host()
+        data = self.data.reshape(-1)
+        if self.dtype is Storage.FLOAT:
+            fun = lib.pysdm_b200_minmax_f64
+        elif self.dtype is Storage.INT:
+            fun = lib.pysdm_b200_minmax_i64
+        else:
+            raise NotImplementedError()
+        _lib.check(fun(ptr(data), data.numel(), int(is_max), box.data_ptr(), ptr(scratch), stream()),
+                   "minmax")
+        if self.dtype is Storage.FLOAT:
+            if int(box[1]) != 0:
+                return float("nan")  # numpy's amin/amax propagate NaN
+            return float(box[:1].view(torch.float64)[0])
+        return int(box[0])
+
+    def amin(self):
+        return self._minmax(False)
+
+    def amax(self):
+        return self._minmax(True)
+
+    def all(self):
+        return bool(torch.all(self.data != 0).item())
+
+    def __bool__(self):
+        if len(self) == 1:
+            return bool(self.data[0].item() != 0)
+        raise NotImplementedError("Logic value of array is ambiguous.")
+
+    # ---- memory plumbing ---------------------------------------------------------------
+    def detach(self):
+        if self.data._base is not None:  # pylint: disable=protected-access
+            self.data = self.data.clone()
+
+    def download(self, target, reshape=False):
+        host = self.data.cpu().numpy()
+        if reshape:
+            host = host.reshape(target.shape)
+        np.copyto(target, host, casting="safe")
+
+    def to_ndarray(self):
+        return self.data.cpu().numpy().copy()
+
+    def upload(self, data):
+        host = np.ascontiguousarray(np.asarray(data).astype(self.dtype, casting="safe"))
+        self.data.copy_(torch.from_numpy(host).reshape(self.data.shape))
+
+    def ravel(self, other):
+        src = other.data if isinstance(other, Storage) else torch.from_numpy(
+            np.ascontiguousarray(other)).to(DEVICE)
+        self.data[:] = src.reshape(-1)
+
+    def urand(self, generator):
+        generator(self)
+
+    def fill(self, other):
+        if isinstance(other, Storage):
+            self.data[:] = other.data
+        else:
+            self.data[:] = other
+
+
+def host_int_result():
+    """pinned int64 mailbox pointer for C-ABI calls that return a host integer"""
+    box = SCRATCH.host()
+    return box, ctypes.c_void_p(box.data_ptr())

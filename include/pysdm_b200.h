@@ -1,0 +1,166 @@
+/*
+ * pysdm_b200.h -- C-ABI of libpysdm_b200.so: the SDM collision / coalescence / breakup
+ * path of PySDM as hand-written CUDA for sm_100a (NVIDIA B200).
+ *
+ * This is the drop-in boundary.  Each entry point replaces one method of the
+ * reference's backend classes (the "L1 backend" of PySDM: the mix-ins listed in
+ * PySDM/backends/numba.py:18-33); the reference method is cited next to it as
+ * file:line, paths relative to PySDM/backends/impl_numba/ unless they start with PySDM/.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name starts with `host_`;
+ *   - floats are fp64, integers int64, flags 1-byte bools (storage.py:16-19);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); calls are
+ *     asynchronous unless they have a `host_` out-parameter, in which case the stream
+ *     is synchronised before returning;
+ *   - the return value is 0 or a cudaError_t;
+ *   - no entry point allocates: scratch is caller-provided (`*_workspace_bytes`);
+ *   - nothing here touches host memory other than `host_*` out-parameters and there is
+ *     no CPU implementation behind any symbol.
+ */
+#ifndef PYSDM_B200_H
+#define PYSDM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- index methods: methods/index_methods.py --------------------------------------- */
+
+/* identity_index, index_methods.py:13-20 */
+int pysdm_b200_identity_index(int64_t *idx, int64_t n, void *stream);
+
+/* shuffle_global, index_methods.py:22-30 (serial swap chain i = length-1 .. 1,
+ * j = int(u01[i] * (i + 1))); replayed bit-exactly in parallel. */
+size_t pysdm_b200_shuffle_workspace_bytes(int64_t length);
+int pysdm_b200_shuffle_global(int64_t *idx, int64_t length, const double *u01, void *ws,
+                              size_t ws_bytes, void *stream);
+
+/* shuffle_local, index_methods.py:32-44 (one swap chain per cell, j drawn over the
+ * whole cell); `length` = cell_start[n_cell]. */
+int pysdm_b200_shuffle_local(int64_t *idx, const double *u01, const int64_t *cell_start,
+                             int64_t n_cell, int64_t length, void *ws, size_t ws_bytes,
+                             void *stream);
+
+/* CellCaretaker.__call__, methods/collisions_methods.py:608-629 with the counting sorts
+ * :682-741: stable sort of idx[:length] by cell_idx[cell_id[idx[i]]] into new_idx and
+ * cell_start[0..n_cell] (exclusive prefix sums).  The caller swaps idx <-> new_idx. */
+size_t pysdm_b200_sort_by_cell_workspace_bytes(int64_t length);
+int pysdm_b200_sort_by_cell_id(int64_t *new_idx, const int64_t *idx, const int64_t *cell_id,
+                               const int64_t *cell_idx, int64_t length, int64_t *cell_start,
+                               int64_t n_cell, void *ws, size_t ws_bytes, void *stream);
+
+/* sort_by_key, index_methods.py:46-48: idx[:] = argsort(attr, stable)[::-1] */
+size_t pysdm_b200_sort_by_key_workspace_bytes(int64_t n);
+int pysdm_b200_sort_by_key(int64_t *idx, const double *attr, int64_t n, void *ws,
+                           size_t ws_bytes, void *stream);
+
+/* remove_zero_n_or_flagged, methods/collisions_methods.py:664-680: the reference's
+ * serial swap-with-last compaction, same surviving order; new length -> *host_new_length */
+size_t pysdm_b200_remove_zero_workspace_bytes(int64_t length);
+int pysdm_b200_remove_zero_n_or_flagged(const int64_t *multiplicity, int64_t *idx,
+                                        int64_t length, int64_t n_sd,
+                                        int64_t *host_new_length, void *ws, size_t ws_bytes,
+                                        void *stream);
+
+/* cell_id, methods/collisions_methods.py:407-416: cell_id = strides . cell_origin;
+ * cell_origin is [n_dims, n_sd] row-major */
+int pysdm_b200_cell_id(int64_t *cell_id, const int64_t *cell_origin, const int64_t *strides,
+                       int64_t n_dims, int64_t n_sd, void *stream);
+
+/* ---- pair methods: methods/pair_methods.py ----------------------------------------- */
+
+/* find_pairs, pair_methods.py:34-55 */
+int pysdm_b200_find_pairs(const int64_t *cell_start, uint8_t *is_first_in_pair,
+                          const int64_t *cell_id, const int64_t *cell_idx, const int64_t *idx,
+                          int64_t length, void *stream);
+
+/* sort_within_pair_by_attr, pair_methods.py:126-140; attr is int64 (attr_is_int) or fp64 */
+int pysdm_b200_sort_within_pair_by_attr(int64_t *idx, int64_t length,
+                                        const uint8_t *is_first_in_pair, const void *attr,
+                                        int attr_is_int, void *stream);
+
+/* {distance,max,min,sum,multiply}_pair, pair_methods.py:14-32,57-95,142-180
+ * op: 0 distance, 1 max, 2 min, 3 sum, 4 multiply; the whole out[0..out_len) is zeroed
+ * first, like the reference does */
+int pysdm_b200_pair_op(int op, double *out, int64_t out_len, const void *in, int in_is_int,
+                       const uint8_t *is_first_in_pair, const int64_t *idx, int64_t length,
+                       void *stream);
+
+/* sort_pair, pair_methods.py:97-124 */
+int pysdm_b200_sort_pair(double *out, int64_t out_len, const double *in,
+                         const uint8_t *is_first_in_pair, const int64_t *idx, int64_t length,
+                         void *stream);
+
+/* ---- collision methods: methods/collisions_methods.py ------------------------------ */
+
+/* normalize, collisions_methods.py:633-662 (caller PySDM/particulator.py:87-96).
+ * prob[d] *= norm_factor[cell_idx[cell_id[d]]], d = pair slot (reference behaviour) */
+int pysdm_b200_normalize(double *prob, int64_t prob_len, const int64_t *cell_id,
+                         const int64_t *cell_idx, const int64_t *cell_start, int64_t n_cell,
+                         double *norm_factor, double timestep, double dv, void *stream);
+
+/* compute_gamma, collisions_methods.py:522-585; `out` may alias `prob` */
+int pysdm_b200_compute_gamma(const double *prob, const double *rand, const int64_t *idx,
+                             int64_t length, const int64_t *multiplicity,
+                             const int64_t *cell_id, int64_t *collision_rate_deficit,
+                             int64_t *collision_rate, const uint8_t *is_first_in_pair,
+                             double *out, void *stream);
+
+/* scale_prob_for_adaptive_sdm_gamma, collisions_methods.py:330-405;
+ * dt_todo: scratch of n_cell doubles (the reference allocates it per call, :355) */
+int pysdm_b200_scale_prob_for_adaptive_sdm_gamma(
+    double *prob, const int64_t *idx, int64_t length, const int64_t *multiplicity,
+    const int64_t *cell_id, double *dt_left, int64_t n_cell, double dt, double dt_min,
+    double dt_max, const uint8_t *is_first_in_pair, int64_t *stats_n_substep,
+    double *stats_dt_min, double *dt_todo, void *stream);
+
+/* adaptive_sdm_end, collisions_methods.py:313-328 -> *host_result */
+int pysdm_b200_adaptive_sdm_end(const double *dt_left, int64_t n_cell,
+                                const int64_t *cell_start, int64_t *host_result,
+                                int64_t *dev_scratch, void *stream);
+
+/* collision_coalescence, collisions_methods.py:418-477 (+ coalesce :44-59,
+ * flag_zero_multiplicity :38-41); attributes is [n_attr, n_sd] row-major */
+int pysdm_b200_collision_coalescence(int64_t *multiplicity, const int64_t *idx, int64_t length,
+                                     double *attributes, int64_t n_attr, int64_t n_sd,
+                                     const double *gamma, int64_t *healthy,
+                                     const int64_t *cell_id, int64_t *coalescence_rate,
+                                     const uint8_t *is_first_in_pair, void *stream);
+
+/* ---- Storage arithmetic: storage.py:54-100,203-213, storage_impl.py:11-83 ---------- */
+/* op: 0 add 1 sub 2 mul 3 div 4 div_if_not_zero 5 pow(sign(x)|x|^s) 6 axpy(a + s*b)
+ *     7 floor 8 exp 9 abs 10 mod; b == NULL selects the scalar operand */
+int pysdm_b200_elementwise(int op, double *out, const double *a, const double *b,
+                           double scalar, int64_t n, void *stream);
+int pysdm_b200_row_modulo(double *out, const double *divisor, int64_t n_rows, int64_t n_cols,
+                          void *stream);
+/* Storage.amin / amax (storage.py:109-119): result -> host_result[0]; host_result[1] != 0
+ * when a NaN was seen (numpy propagates NaN) */
+size_t pysdm_b200_reduce_scratch_bytes(void);
+int pysdm_b200_minmax_f64(const double *in, int64_t n, int is_max, double *host_result,
+                          void *scratch, void *stream);
+int pysdm_b200_minmax_i64(const int64_t *in, int64_t n, int is_max, int64_t *host_result,
+                          void *scratch, void *stream);
+
+/* ---- Random: random.py:9-19 (call contract); Philox4x32-10 counter-based generator --- */
+int pysdm_b200_philox_uniform(double *out, int64_t n, uint64_t seed, uint64_t call,
+                              void *stream);
+int pysdm_b200_philox_raw(uint32_t *dev_out4, uint32_t c0, uint32_t c1, uint32_t c2,
+                          uint32_t c3, uint32_t k0, uint32_t k1, void *stream);
+
+/* ---- physics: methods/physics_methods.py:107-133 ----------------------------------- */
+int pysdm_b200_volume_of_water_mass(double *volume, const double *mass, int64_t n,
+                                    double rho_w, void *stream);
+int pysdm_b200_mass_of_water_volume(double *mass, const double *volume, int64_t n,
+                                    double rho_w, void *stream);
+
+/* PYSDM_B200_H_END_OF_METHOD_LEVEL -- fused step and later additions follow */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYSDM_B200_H */

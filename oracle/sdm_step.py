@@ -39,7 +39,7 @@ class Golovin:
         self.b = b
 
     def __call__(self, box, output, flag):
-        orc.pair_op("sum", output, box.volume(), flag, box.idx, box.length)
+        box.be.pair_op("sum", output, box.volume(), flag, box.idx, box.length)
         output *= self.b
 
 
@@ -48,8 +48,12 @@ class OracleCollision:  # pylint: disable=too-many-instance-attributes
 
     def __init__(self, *, multiplicity, water_mass, cell_id=None, n_cell=1, dt, dv, kernel,
                  seed, adaptive=False, substeps=1, dt_coal_range=(0.1, 100.0), croupier="local",
-                 optimized_random=False, rho_w=1000.0, extra_attributes=None, rnd=None):
+                 optimized_random=False, rho_w=1000.0, extra_attributes=None, rnd=None, be=None):
         assert substeps == 1 or adaptive is False
+        # `be`: module with the signatures of oracle/sdm_oracle.py (tests plug the CUDA
+        # adapter in here to drive the device kernels through the very same step logic)
+        self.be = be or orc
+        self.kernel_be = self.be
         self.n_sd = len(multiplicity)
         self.n_cell = n_cell
         self.dt, self.dv, self.kernel, self.rho_w = dt, dv, kernel, rho_w
@@ -98,11 +102,11 @@ class OracleCollision:  # pylint: disable=too-many-instance-attributes
 
     # ---- attributes -------------------------------------------------------------
     def volume(self):
-        orc.volume_of_water_mass(self._volume, self.attributes[0], self.rho_w)
+        self.be.volume_of_water_mass(self._volume, self.attributes[0], self.rho_w)
         return self._volume
 
     def sort_by_cell_id(self):
-        orc.counting_sort_by_cell_id(self.tmp_idx, self.idx, self.cell_id, self.cell_idx,
+        self.be.counting_sort_by_cell_id(self.tmp_idx, self.idx, self.cell_id, self.cell_idx,
                                      self.length, self.cell_start)
         self.idx, self.tmp_idx = self.tmp_idx, self.idx
         self.sorted = True
@@ -115,7 +119,7 @@ class OracleCollision:  # pylint: disable=too-many-instance-attributes
     def sanitize(self):
         if not self.healthy[0]:
             self.length = self.valid_n_sd
-            self.length = orc.remove_zero_n_or_flagged(self.multiplicity, self.idx, self.length)
+            self.length = self.be.remove_zero_n_or_flagged(self.multiplicity, self.idx, self.length)
             self.valid_n_sd = self.length
             self.healthy[0] = 1
             self.sorted = False
@@ -123,9 +127,9 @@ class OracleCollision:  # pylint: disable=too-many-instance-attributes
     def permutation(self, u01, local):
         if local:
             cell_start = self.get_cell_start()  # may swap self.idx <-> self.tmp_idx
-            orc.shuffle_local(self.idx, u01, cell_start)
+            self.be.shuffle_local(self.idx, u01, cell_start)
         else:
-            orc.shuffle_global(self.idx, self.length, u01)
+            self.be.shuffle_global(self.idx, self.length, u01)
             self.sorted = False
 
     # ---- random numbers -----------------------------------------------------------
@@ -150,13 +154,13 @@ class OracleCollision:  # pylint: disable=too-many-instance-attributes
         else:
             self.dt_left[:] = self.dt
             while self.length != 0:
-                orc.sort_by_key(self.cell_idx, self.dt_left)
+                self.be.sort_by_key(self.cell_idx, self.dt_left)
                 self.step()
-                end = orc.adaptive_sdm_end(self.dt_left, self.get_cell_start())
+                end = self.be.adaptive_sdm_end(self.dt_left, self.get_cell_start())
                 assert end <= self.length
                 self.length = end
             self.length = self.valid_n_sd
-            orc.identity_index(self.cell_idx)
+            self.be.identity_index(self.cell_idx)
             self.sort_by_cell_id()
         self.substep = 0
 
@@ -165,18 +169,18 @@ class OracleCollision:  # pylint: disable=too-many-instance-attributes
         # toss_candidate_pairs_and_sort_within_pair_by_multiplicity
         self.permutation(pairs_rand, self.croupier == "local")
         cell_start = self.get_cell_start()
-        orc.find_pairs(cell_start, self.flag, self.cell_id, self.cell_idx, self.idx, self.length)
-        orc.sort_within_pair_by_attr(self.idx, self.length, self.flag, self.multiplicity)
+        self.be.find_pairs(cell_start, self.flag, self.cell_id, self.cell_idx, self.idx, self.length)
+        self.be.sort_within_pair_by_attr(self.idx, self.length, self.flag, self.multiplicity)
         # compute_probabilities_of_collision
         prob = self.gamma
         self.kernel(self, self.kernel_temp, self.flag)
-        orc.pair_op("max", prob, self.multiplicity, self.flag, self.idx, self.length)
+        self.be.pair_op("max", prob, self.multiplicity, self.flag, self.idx, self.length)
         prob *= self.kernel_temp
-        orc.normalize(prob, self.cell_id, self.cell_idx, self.get_cell_start(), self.norm_factor,
+        self.be.normalize(prob, self.cell_id, self.cell_idx, self.get_cell_start(), self.norm_factor,
                       self.dt, self.dv)
         # compute_gamma
         if self.adaptive:
-            orc.scale_prob_for_adaptive_sdm_gamma(prob, self.idx, self.length, self.multiplicity,
+            self.be.scale_prob_for_adaptive_sdm_gamma(prob, self.idx, self.length, self.multiplicity,
                                                   self.cell_id, self.dt_left, self.dt,
                                                   self.dt_coal_range, self.flag,
                                                   self.stats_n_substep, self.stats_dt_min)
@@ -184,10 +188,10 @@ class OracleCollision:  # pylint: disable=too-many-instance-attributes
                 self.dt_min_warning = True
         else:
             prob /= self.substeps
-        orc.compute_gamma(prob, rand, self.idx, self.length, self.multiplicity, self.cell_id,
+        self.be.compute_gamma(prob, rand, self.idx, self.length, self.multiplicity, self.cell_id,
                           self.collision_rate_deficit, self.collision_rate, self.flag, self.gamma)
         # collision_coalescence_breakup
-        orc.collision_coalescence(self.multiplicity, self.idx, self.length, self.attributes,
+        self.be.collision_coalescence(self.multiplicity, self.idx, self.length, self.attributes,
                                   self.gamma, self.healthy, self.cell_id, self.coalescence_rate,
                                   self.flag)
         self.sanitize()

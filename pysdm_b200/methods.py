@@ -1,0 +1,212 @@
+"""Tensor-level host bindings of the C-ABI (include/pysdm_b200.h): one Python function per
+reference backend method, same names and argument order as the reference's Numba
+`*Methods` bodies (PySDM/backends/impl_numba/methods/{index,pair,collisions,physics}_methods.py),
+operating in place on CUDA tensors (torch is only the device-memory handle).
+
+No CPU path: every function launches kernels of libpysdm_b200.so and raises if the
+library is missing or a tensor does not live on a CUDA device.
+"""
+
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import PAIR_OPS, check
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t, dtype=None):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise _lib.CudaLibraryError("pysdm_b200 has no CPU path: tensor is not on a CUDA device")
+    assert t.is_contiguous(), "non-contiguous device view"
+    if dtype is not None:
+        assert t.dtype == dtype, (t.dtype, dtype)
+    return t.data_ptr()
+
+
+def _pi(t):
+    return _p(t, torch.int64)
+
+
+def _pf(t):
+    return _p(t, torch.float64)
+
+
+def _pb(t):
+    assert t.dtype in (torch.bool, torch.uint8)
+    return _p(t)
+
+
+class Workspace:
+    """grow-only device scratch (per key) + pinned mailbox for host results"""
+
+    def __init__(self):
+        self._dev = {}
+        self._box = None
+
+    def dev(self, key, nbytes, device):
+        buf = self._dev.get((key, device))
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=device)
+            self._dev[(key, device)] = buf
+        return buf
+
+    def box(self):
+        if self._box is None:
+            self._box = torch.zeros(4, dtype=torch.int64).pin_memory()
+        return self._box
+
+
+WS = Workspace()
+
+
+# ---- index methods ------------------------------------------------------------------
+def identity_index(idx):
+    check(_lib.load().pysdm_b200_identity_index(_pi(idx), idx.numel(), _stream()), "identity_index")
+
+
+def shuffle_global(idx, length, u01):
+    lib = _lib.load()
+    nbytes = lib.pysdm_b200_shuffle_workspace_bytes(int(length))
+    ws = WS.dev("shuffle", nbytes, idx.device)
+    check(lib.pysdm_b200_shuffle_global(_pi(idx), int(length), _pf(u01), _p(ws), ws.numel(),
+                                        _stream()), "shuffle_global")
+
+
+def shuffle_local(idx, u01, cell_start, length=None):
+    """`length` = cell_start[-1]; pass it when known on the host to avoid a device sync"""
+    lib = _lib.load()
+    if length is None:
+        length = int(cell_start[-1].item())
+    nbytes = lib.pysdm_b200_shuffle_workspace_bytes(int(length))
+    ws = WS.dev("shuffle", nbytes, idx.device)
+    check(lib.pysdm_b200_shuffle_local(_pi(idx), _pf(u01), _pi(cell_start),
+                                       cell_start.numel() - 1, int(length), _p(ws), ws.numel(),
+                                       _stream()), "shuffle_local")
+
+
+def sort_by_key(idx, attr):
+    lib = _lib.load()
+    n = attr.numel()
+    ws = WS.dev("sort_by_key", lib.pysdm_b200_sort_by_key_workspace_bytes(n), idx.device)
+    check(lib.pysdm_b200_sort_by_key(_pi(idx), _pf(attr), n, _p(ws), ws.numel(), _stream()),
+          "sort_by_key")
+
+
+def remove_zero_n_or_flagged(multiplicity, idx, length):
+    lib = _lib.load()
+    ws = WS.dev("remove_zero", lib.pysdm_b200_remove_zero_workspace_bytes(int(length)), idx.device)
+    box = WS.box()
+    check(lib.pysdm_b200_remove_zero_n_or_flagged(
+        _pi(multiplicity), _pi(idx), int(length), idx.numel(), box.data_ptr(), _p(ws), ws.numel(),
+        _stream()), "remove_zero_n_or_flagged")
+    return int(box[0])
+
+
+def counting_sort_by_cell_id(new_idx, idx, cell_id, cell_idx, length, cell_start):
+    lib = _lib.load()
+    ws = WS.dev("sort_by_cell", lib.pysdm_b200_sort_by_cell_workspace_bytes(int(length)),
+                idx.device)
+    check(lib.pysdm_b200_sort_by_cell_id(
+        _pi(new_idx), _pi(idx), _pi(cell_id), _pi(cell_idx), int(length), _pi(cell_start),
+        cell_start.numel() - 1, _p(ws), ws.numel(), _stream()), "sort_by_cell_id")
+
+
+def cell_id(cell_id_out, cell_origin, strides):
+    n_dims, n_sd = cell_origin.shape
+    strides = strides.reshape(-1).contiguous()
+    check(_lib.load().pysdm_b200_cell_id(_pi(cell_id_out), _pi(cell_origin), _pi(strides), n_dims,
+                                         n_sd, _stream()), "cell_id")
+
+
+# ---- pair methods ---------------------------------------------------------------------
+def find_pairs(cell_start, is_first_in_pair, cell_id_, cell_idx, idx, length):
+    check(_lib.load().pysdm_b200_find_pairs(_pi(cell_start), _pb(is_first_in_pair), _pi(cell_id_),
+                                            _pi(cell_idx), _pi(idx), int(length), _stream()),
+          "find_pairs")
+
+
+def sort_within_pair_by_attr(idx, length, is_first_in_pair, attr):
+    is_int = attr.dtype == torch.int64
+    check(_lib.load().pysdm_b200_sort_within_pair_by_attr(
+        _pi(idx), int(length), _pb(is_first_in_pair), _p(attr), int(is_int), _stream()),
+        "sort_within_pair_by_attr")
+
+
+def pair_op(op, data_out, data_in, is_first_in_pair, idx, length):
+    is_int = data_in.dtype == torch.int64
+    check(_lib.load().pysdm_b200_pair_op(
+        PAIR_OPS[op], _pf(data_out), data_out.numel(), _p(data_in), int(is_int),
+        _pb(is_first_in_pair), _pi(idx), int(length), _stream()), op + "_pair")
+
+
+def sort_pair(data_out, data_in, is_first_in_pair, idx, length):
+    check(_lib.load().pysdm_b200_sort_pair(_pf(data_out), data_out.numel(), _pf(data_in),
+                                           _pb(is_first_in_pair), _pi(idx), int(length),
+                                           _stream()), "sort_pair")
+
+
+# ---- physics -----------------------------------------------------------------------------
+def volume_of_water_mass(volume, mass, rho_w):
+    check(_lib.load().pysdm_b200_volume_of_water_mass(_pf(volume), _pf(mass), volume.numel(),
+                                                      float(rho_w), _stream()), "volume")
+
+
+def mass_of_water_volume(mass, volume, rho_w):
+    check(_lib.load().pysdm_b200_mass_of_water_volume(_pf(mass), _pf(volume), volume.numel(),
+                                                      float(rho_w), _stream()), "mass")
+
+
+# ---- collisions ----------------------------------------------------------------------------
+def normalize(prob, cell_id_, cell_idx, cell_start, norm_factor, timestep, dv):
+    check(_lib.load().pysdm_b200_normalize(
+        _pf(prob), prob.numel(), _pi(cell_id_), _pi(cell_idx), _pi(cell_start),
+        cell_start.numel() - 1, _pf(norm_factor), float(timestep), float(dv), _stream()),
+        "normalize")
+
+
+def compute_gamma(prob, rand, idx, length, multiplicity, cell_id_, collision_rate_deficit,
+                  collision_rate, is_first_in_pair, out):
+    check(_lib.load().pysdm_b200_compute_gamma(
+        _pf(prob), _pf(rand), _pi(idx), int(length), _pi(multiplicity), _pi(cell_id_),
+        _pi(collision_rate_deficit), _pi(collision_rate), _pb(is_first_in_pair), _pf(out),
+        _stream()), "compute_gamma")
+
+
+def collision_coalescence(multiplicity, idx, length, attributes, gamma, healthy, cell_id_,
+                          coalescence_rate, is_first_in_pair):
+    n_attr, n_sd = attributes.shape
+    check(_lib.load().pysdm_b200_collision_coalescence(
+        _pi(multiplicity), _pi(idx), int(length), _pf(attributes), n_attr, n_sd, _pf(gamma),
+        _pi(healthy), _pi(cell_id_), _pi(coalescence_rate), _pb(is_first_in_pair), _stream()),
+        "collision_coalescence")
+
+
+def adaptive_sdm_end(dt_left, cell_start):
+    box = WS.box()
+    scratch = WS.dev("adaptive_end", 64, dt_left.device)
+    check(_lib.load().pysdm_b200_adaptive_sdm_end(
+        _pf(dt_left), dt_left.numel(), _pi(cell_start), box.data_ptr(), _p(scratch), _stream()),
+        "adaptive_sdm_end")
+    return int(box[0])
+
+
+def scale_prob_for_adaptive_sdm_gamma(prob, idx, length, multiplicity, cell_id_, dt_left, dt,
+                                      dt_range, is_first_in_pair, stats_n_substep, stats_dt_min):
+    n_cell = dt_left.numel()
+    dt_todo = WS.dev("dt_todo", 8 * n_cell, dt_left.device)
+    check(_lib.load().pysdm_b200_scale_prob_for_adaptive_sdm_gamma(
+        _pf(prob), _pi(idx), int(length), _pi(multiplicity), _pi(cell_id_), _pf(dt_left), n_cell,
+        float(dt), float(dt_range[0]), float(dt_range[1]), _pb(is_first_in_pair),
+        _pi(stats_n_substep), _pf(stats_dt_min), _p(dt_todo), _stream()),
+        "scale_prob_for_adaptive_sdm_gamma")
+
+
+def host_ptr(tensor):
+    return ctypes.c_void_p(tensor.data_ptr())

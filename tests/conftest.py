@@ -31,3 +31,16 @@ def golden_methods():
     import numpy as np  # pylint: disable=import-outside-toplevel
 
     return np.load(os.path.join(GOLDEN, "methods.npz"))
+
+
+@pytest.fixture(params=["oracle", pytest.param("cuda", marks=pytest.mark.gpu)])
+def be(request):
+    """module with the oracle's call signatures: the C oracle itself, or the CUDA kernels
+    behind the C-ABI (numpy in/out adapter)"""
+    if request.param == "oracle":
+        from oracle import sdm_oracle  # pylint: disable=import-outside-toplevel
+
+        return sdm_oracle
+    from . import device_adapter  # pylint: disable=import-outside-toplevel
+
+    return device_adapter

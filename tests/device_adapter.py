@@ -1,0 +1,153 @@
+"""numpy-in / numpy-out adapter around pysdm_b200.methods (the C-ABI bindings) with the
+call signatures of oracle/sdm_oracle.py, so that one test body checks both the CPU
+oracle and the CUDA path against the same golden vectors.  Arrays are uploaded, the
+CUDA kernels run, and the (in-place) results are copied back into the caller's arrays."""
+
+import numpy as np
+import torch
+
+from pysdm_b200 import methods as dev
+
+DEVICE = "cuda"
+
+
+class _Mirror:
+    """uploads numpy arrays on entry; copies the mutated ones back on exit"""
+
+    def __init__(self, *arrays):
+        self.host = arrays
+        self.dev = [torch.from_numpy(np.ascontiguousarray(a)).to(DEVICE) for a in arrays]
+
+    def back(self, *which):
+        torch.cuda.synchronize()
+        for i in which:
+            h = self.host[i]
+            d = self.dev[i].cpu().numpy()
+            h[...] = d.view(h.dtype) if d.dtype != h.dtype else d
+
+
+def _run(fun, arrays, mutated, *extra_before, **kw):
+    m = _Mirror(*arrays)
+    out = fun(*m.dev, **kw)
+    m.back(*mutated)
+    return out
+
+
+def identity_index(idx):
+    _run(dev.identity_index, (idx,), (0,))
+
+
+def shuffle_global(idx, length, u01):
+    m = _Mirror(idx, u01)
+    dev.shuffle_global(m.dev[0], length, m.dev[1])
+    m.back(0)
+
+
+def shuffle_local(idx, u01, cell_start):
+    m = _Mirror(idx, u01, cell_start)
+    dev.shuffle_local(m.dev[0], m.dev[1], m.dev[2], int(cell_start[-1]))
+    m.back(0)
+
+
+def sort_by_key(idx, attr):
+    _run(dev.sort_by_key, (idx, attr), (0,))
+
+
+def remove_zero_n_or_flagged(multiplicity, idx, length):
+    m = _Mirror(multiplicity, idx)
+    n = dev.remove_zero_n_or_flagged(m.dev[0], m.dev[1], length)
+    m.back(1)
+    return n
+
+
+def counting_sort_by_cell_id(new_idx, idx, cell_id, cell_idx, length, cell_start):
+    m = _Mirror(new_idx, idx, cell_id, cell_idx, cell_start)
+    dev.counting_sort_by_cell_id(m.dev[0], m.dev[1], m.dev[2], m.dev[3], length, m.dev[4])
+    m.back(0, 4)
+
+
+def cell_id(cell_id_out, cell_origin, strides):
+    m = _Mirror(cell_id_out, np.ascontiguousarray(cell_origin, dtype=np.int64),
+                np.ascontiguousarray(np.asarray(strides, dtype=np.int64).ravel()))
+    dev.cell_id(m.dev[0], m.dev[1], m.dev[2])
+    m.back(0)
+
+
+def find_pairs(cell_start, is_first_in_pair, cell_id_, cell_idx, idx, length):
+    m = _Mirror(cell_start, is_first_in_pair, cell_id_, cell_idx, idx)
+    dev.find_pairs(m.dev[0], m.dev[1], m.dev[2], m.dev[3], m.dev[4], length)
+    m.back(1)
+
+
+def sort_within_pair_by_attr(idx, length, is_first_in_pair, attr):
+    m = _Mirror(idx, is_first_in_pair, attr)
+    dev.sort_within_pair_by_attr(m.dev[0], length, m.dev[1], m.dev[2])
+    m.back(0)
+
+
+def pair_op(op, data_out, data_in, is_first_in_pair, idx, length):
+    m = _Mirror(data_out, data_in, is_first_in_pair, idx)
+    dev.pair_op(op, m.dev[0], m.dev[1], m.dev[2], m.dev[3], length)
+    m.back(0)
+
+
+def sort_pair(data_out, data_in, is_first_in_pair, idx, length):
+    m = _Mirror(data_out, data_in, is_first_in_pair, idx)
+    dev.sort_pair(m.dev[0], m.dev[1], m.dev[2], m.dev[3], length)
+    m.back(0)
+
+
+def volume_of_water_mass(volume, mass, rho_w):
+    m = _Mirror(volume, mass)
+    dev.volume_of_water_mass(m.dev[0], m.dev[1], rho_w)
+    m.back(0)
+
+
+def mass_of_water_volume(mass, volume, rho_w):
+    m = _Mirror(mass, volume)
+    dev.mass_of_water_volume(m.dev[0], m.dev[1], rho_w)
+    m.back(0)
+
+
+def normalize(prob, cell_id_, cell_idx, cell_start, norm_factor, timestep, dv):
+    m = _Mirror(prob, cell_id_, cell_idx, cell_start, norm_factor)
+    dev.normalize(m.dev[0], m.dev[1], m.dev[2], m.dev[3], m.dev[4], timestep, dv)
+    m.back(0, 4)
+
+
+def compute_gamma(prob, rand, idx, length, multiplicity, cell_id_, collision_rate_deficit,
+                  collision_rate, is_first_in_pair, out):
+    alias = out is prob
+    m = _Mirror(prob, rand, idx, multiplicity, cell_id_, collision_rate_deficit, collision_rate,
+                is_first_in_pair, out)
+    d = m.dev
+    dev.compute_gamma(d[0], d[1], d[2], length, d[3], d[4], d[5], d[6], d[7],
+                      d[0] if alias else d[8])
+    if alias:
+        m.back(0, 5, 6)
+    else:
+        m.back(5, 6, 8)
+
+
+def collision_coalescence(multiplicity, idx, length, attributes, gamma, healthy, cell_id_,
+                          coalescence_rate, is_first_in_pair):
+    m = _Mirror(multiplicity, idx, attributes, gamma, healthy, cell_id_, coalescence_rate,
+                is_first_in_pair)
+    d = m.dev
+    dev.collision_coalescence(d[0], d[1], length, d[2], d[3], d[4], d[5], d[6], d[7])
+    m.back(0, 2, 4, 6)
+
+
+def adaptive_sdm_end(dt_left, cell_start):
+    m = _Mirror(dt_left, cell_start)
+    return dev.adaptive_sdm_end(m.dev[0], m.dev[1])
+
+
+def scale_prob_for_adaptive_sdm_gamma(prob, idx, length, multiplicity, cell_id_, dt_left, dt,
+                                      dt_range, is_first_in_pair, stats_n_substep, stats_dt_min):
+    m = _Mirror(prob, idx, multiplicity, cell_id_, dt_left, is_first_in_pair, stats_n_substep,
+                stats_dt_min)
+    d = m.dev
+    dev.scale_prob_for_adaptive_sdm_gamma(d[0], d[1], length, d[2], d[3], d[4], dt, dt_range,
+                                          d[5], d[6], d[7])
+    m.back(0, 4, 6, 7)

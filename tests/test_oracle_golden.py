@@ -1,4 +1,5 @@
-"""CPU: the C oracle against vectors produced by the reference itself
+"""The C oracle (CPU) and, with `-m gpu`, the CUDA method-level kernels through the
+C-ABI (tests/device_adapter.py), both against vectors produced by the reference itself
 (tests/golden/*.npz, made by oracle/gen_golden.py from PySDM's Numba backend with
 Formulae(fastmath=False)) and against the known-answer vectors quoted in the
 reference's own unit tests.  Bit-exact everywhere."""
@@ -38,29 +39,29 @@ def test_pair_indices_truth_table(i, idx, flag, gamma, expected):
     ((4, 5, 4.5, 0, 0), (0, 1, 2, 3, 4, 5), 3),
     ((4, 5, 4.5, 3, 0.1), (0, 1, 2, 3, 4, 5), 5),
 ))
-def test_adaptive_sdm_end_vectors(dt_left, cell_start, expected):
-    assert orc.adaptive_sdm_end(np.asarray(dt_left, dtype=np.float64),
+def test_adaptive_sdm_end_vectors(be, dt_left, cell_start, expected):
+    assert be.adaptive_sdm_end(np.asarray(dt_left, dtype=np.float64),
                                 np.asarray(cell_start, dtype=np.int64)) == expected
 
 
 U01 = np.asarray([0.1, 0.4, 0.2, 0.5, 0.9, 0.1, 0.6, 0.3])
 
 
-def test_shuffle_global_vector():
+def test_shuffle_global_vector(be):
     # tests/unit_tests/impl/test_particle_attributes.py:149-171
     idx = np.arange(8, dtype=np.int64)
-    orc.shuffle_global(idx, 8, U01)
+    be.shuffle_global(idx, 8, U01)
     np.testing.assert_array_equal(idx, [1, 3, 5, 7, 6, 0, 4, 2])
 
 
-def test_shuffle_local_vector():
+def test_shuffle_local_vector(be):
     # tests/unit_tests/impl/test_particle_attributes.py:173-201
     idx = np.arange(8, dtype=np.int64)
-    orc.shuffle_local(idx, U01, np.asarray([0, 0, 2, 5, 7, 8], dtype=np.int64))
+    be.shuffle_local(idx, U01, np.asarray([0, 0, 2, 5, 7, 8], dtype=np.int64))
     np.testing.assert_array_equal(idx, [1, 0, 2, 3, 4, 5, 6, 7])
 
 
-def test_compute_gamma_grid():
+def test_compute_gamma_grid(be):
     # tests/unit_tests/dynamics/collisions/test_sdm_single_cell.py:216-258:
     # gamma = floor(p) + (r < p - floor(p)) on a grid of (prob, rand)
     probs = np.linspace(0, 3, 87)
@@ -72,7 +73,7 @@ def test_compute_gamma_grid():
         flag = np.tile(np.asarray([True, False]), n)
         mult = np.tile(np.asarray([10, 1], dtype=np.int64), n)
         rate, deficit = np.zeros(1, np.int64), np.zeros(1, np.int64)
-        orc.compute_gamma(prob, rands.copy(), idx, 2 * n, mult, np.zeros(2 * n, np.int64),
+        be.compute_gamma(prob, rands.copy(), idx, 2 * n, mult, np.zeros(2 * n, np.int64),
                           deficit, rate, flag, prob)
         expected = np.floor(p) + (rands < p - np.floor(p))
         np.testing.assert_array_equal(prob, expected)
@@ -81,31 +82,31 @@ def test_compute_gamma_grid():
 # ---- method-level vectors from the reference run ---------------------------------------
 @pytest.mark.parametrize("tag", TAGS)
 @pytest.mark.parametrize("scheme", ("counting_sort", "counting_sort_parallel"))
-def test_counting_sort(golden_methods, tag, scheme):
+def test_counting_sort(be, golden_methods, tag, scheme):
     c = case(golden_methods, f"sort_{tag}_{scheme}")
     new_idx = np.full(len(c["idx_in"]), -1, dtype=np.int64)
     cell_start = np.zeros(len(c["cell_start"]), dtype=np.int64)
     length = int(c["length"])
-    orc.counting_sort_by_cell_id(new_idx, c["idx_in"].copy(), c["cell_id"], c["cell_idx"], length,
+    be.counting_sort_by_cell_id(new_idx, c["idx_in"].copy(), c["cell_id"], c["cell_idx"], length,
                                  cell_start)
     np.testing.assert_array_equal(new_idx[:length], c["idx_out"])
     np.testing.assert_array_equal(cell_start, c["cell_start"])
 
 
 @pytest.mark.parametrize("tag", TAGS)
-def test_shuffles(golden_methods, tag):
+def test_shuffles(be, golden_methods, tag):
     c = case(golden_methods, f"shuffle_local_{tag}")
     idx = c["idx_in"].copy()
-    orc.shuffle_local(idx, c["u01"], c["cell_start"])
+    be.shuffle_local(idx, c["u01"], c["cell_start"])
     np.testing.assert_array_equal(idx, c["idx_out"])
     c = case(golden_methods, f"shuffle_global_{tag}")
     idx = c["idx_in"].copy()
-    orc.shuffle_global(idx, int(c["length"]), c["u01"])
+    be.shuffle_global(idx, int(c["length"]), c["u01"])
     np.testing.assert_array_equal(idx, c["idx_out"])
 
 
 @pytest.mark.parametrize("tag", TAGS)
-def test_pair_pipeline(golden_methods, tag):
+def test_pair_pipeline(be, golden_methods, tag):
     """find_pairs -> sort_within_pair -> pair reductions -> normalize -> adaptive
     scaling -> gamma -> coalescence -> remove_zero, each checked on its own vector"""
     g = golden_methods
@@ -113,31 +114,31 @@ def test_pair_pipeline(golden_methods, tag):
     length = int(fp["length"])
     n_sd = len(fp["idx"])
     flag = np.zeros(n_sd, dtype=np.bool_)
-    orc.find_pairs(fp["cell_start"], flag, fp["cell_id"], fp["cell_idx"], fp["idx"], length)
+    be.find_pairs(fp["cell_start"], flag, fp["cell_id"], fp["cell_idx"], fp["idx"], length)
     np.testing.assert_array_equal(flag[:length], fp["flag"][:length])
 
     sw = case(g, f"sort_within_pair_{tag}")
     idx = sw["idx_in"].copy()
-    orc.sort_within_pair_by_attr(idx, length, flag, sw["mult"])
+    be.sort_within_pair_by_attr(idx, length, flag, sw["mult"])
     np.testing.assert_array_equal(idx, sw["idx_out"])
 
     po = case(g, f"pair_ops_{tag}")
     out = np.full(n_sd // 2, np.nan)
     for op in ("distance", "max", "min", "sum", "multiply"):
         out[:] = np.nan
-        orc.pair_op(op, out, po["vol"], flag, idx, length)
+        be.pair_op(op, out, po["vol"], flag, idx, length)
         assert_same_f64(out, g[f"pair_{op}_{tag}/out"], op)
     out[:] = np.nan
-    orc.pair_op("max", out, po["mult"], flag, idx, length)
+    be.pair_op("max", out, po["mult"], flag, idx, length)
     assert_same_f64(out, g[f"pair_max_int_{tag}/out"], "max int")
     outn = np.full(n_sd, np.nan)
-    orc.sort_pair(outn, po["vol"], flag, idx, length)
+    be.sort_pair(outn, po["vol"], flag, idx, length)
     assert_same_f64(outn, po["sort_pair"], "sort_pair")
 
     nm = case(g, f"normalize_{tag}")
     prob = nm["prob_in"].copy()
     norm_factor = np.full(len(fp["cell_idx"]), np.nan)
-    orc.normalize(prob, fp["cell_id"], fp["cell_idx"], fp["cell_start"], norm_factor,
+    be.normalize(prob, fp["cell_id"], fp["cell_idx"], fp["cell_start"], norm_factor,
                   float(nm["timestep"]), float(nm["dv"]))
     assert_same_f64(norm_factor, nm["norm_factor"], "norm_factor")
     assert_same_f64(prob, nm["prob_out"], "normalize")
@@ -148,20 +149,20 @@ def test_pair_pipeline(golden_methods, tag):
         dt_left = ad["dt_left_in"].copy()
         n_substep = ad["n_substep_in"].copy()
         dt_min = ad["dt_min_in"].copy()
-        orc.scale_prob_for_adaptive_sdm_gamma(prob_a, idx, length, po["mult"], fp["cell_id"],
+        be.scale_prob_for_adaptive_sdm_gamma(prob_a, idx, length, po["mult"], fp["cell_id"],
                                               dt_left, float(ad["dt"]), tuple(ad["dt_range"]),
                                               flag, n_substep, dt_min)
         assert_same_f64(prob_a, ad["prob_out"], "adaptive prob")
         assert_same_f64(dt_left, ad["dt_left_out"], "dt_left")
         assert_same_f64(dt_min, ad["dt_min_out"], "stats_dt_min")
         np.testing.assert_array_equal(n_substep, ad["n_substep_out"])
-        assert orc.adaptive_sdm_end(dt_left, fp["cell_start"]) == int(
+        assert be.adaptive_sdm_end(dt_left, fp["cell_start"]) == int(
             g[f"adaptive_end_{tag}_{first}/end"])
 
     gm = case(g, f"gamma_{tag}")
     n_cell = len(fp["cell_idx"])
     rate, deficit = np.zeros(n_cell, np.int64), np.zeros(n_cell, np.int64)
-    orc.compute_gamma(prob, gm["rand"], idx, length, po["mult"], fp["cell_id"], deficit, rate,
+    be.compute_gamma(prob, gm["rand"], idx, length, po["mult"], fp["cell_id"], deficit, rate,
                       flag, prob)
     assert_same_f64(prob, gm["gamma"], "gamma")
     np.testing.assert_array_equal(rate, gm["rate"])
@@ -173,7 +174,7 @@ def test_pair_pipeline(golden_methods, tag):
         mult = po["mult"].copy()
         healthy = np.ones(1, np.int64)
         coal = np.zeros(n_cell, np.int64)
-        orc.collision_coalescence(mult, idx, length, attrs, prob, healthy, fp["cell_id"], coal,
+        be.collision_coalescence(mult, idx, length, attrs, prob, healthy, fp["cell_id"], coal,
                                   flag)
         np.testing.assert_array_equal(mult, co["mult_out"])
         assert_same_f64(attrs, co["attrs_out"], "attributes")
@@ -181,32 +182,32 @@ def test_pair_pipeline(golden_methods, tag):
         np.testing.assert_array_equal(coal, co["coal_rate"])
         rz = case(g, f"remove_zero_{tag}_{n_attr}")
         idx2 = idx.copy()
-        new_length = orc.remove_zero_n_or_flagged(mult, idx2, length)
+        new_length = be.remove_zero_n_or_flagged(mult, idx2, length)
         assert new_length == int(rz["new_length"])
         np.testing.assert_array_equal(idx2, rz["idx_out"])
 
 
 @pytest.mark.parametrize("tag", TAGS)
-def test_sort_by_key_and_cell_id(golden_methods, tag):
+def test_sort_by_key_and_cell_id(be, golden_methods, tag):
     c = case(golden_methods, f"sort_by_key_{tag}")
     out = np.zeros(len(c["keys"]), np.int64)
-    orc.sort_by_key(out, c["keys"])
+    be.sort_by_key(out, c["keys"])
     np.testing.assert_array_equal(out, c["out"])
     c = case(golden_methods, f"cell_id_{tag}")
     out = np.zeros(c["origin"].shape[1], np.int64)
-    orc.cell_id(out, np.ascontiguousarray(c["origin"], dtype=np.int64), c["strides"])
+    be.cell_id(out, np.ascontiguousarray(c["origin"], dtype=np.int64), c["strides"])
     np.testing.assert_array_equal(out, c["out"])
 
 
 # ---- whole time steps ---------------------------------------------------------------------
-def make_oracle_from_scenario(s, name):
+def make_oracle_from_scenario(s, name, be=orc):
     kw = dict(SCENARIO_KW[name])
     return OracleCollision(
         multiplicity=s["init/multiplicity"], water_mass=s["init/signed water mass"],
         cell_id=s["init/cell id"] if "init/cell id" in s.files and int(s["meta/n_cell"]) > 1
         else None,
         n_cell=int(s["meta/n_cell"]), dt=float(s["meta/dt"]), dv=float(s["meta/dv"]),
-        kernel=Golovin(GOLOVIN_B), seed=int(s["meta/seed"]), rho_w=float(s["meta/rho_w"]), **kw)
+        kernel=Golovin(GOLOVIN_B), seed=int(s["meta/seed"]), rho_w=float(s["meta/rho_w"]), be=be, **kw)
 
 
 def check_against_snapshot(sut, s, step):
@@ -223,9 +224,9 @@ def check_against_snapshot(sut, s, step):
 
 
 @pytest.mark.parametrize("name", SCENARIOS)
-def test_scenarios(name):
+def test_scenarios(be, name):
     s = load_scenario(name)
-    sut = make_oracle_from_scenario(s, name)
+    sut = make_oracle_from_scenario(s, name, be)
     for step in range(int(s["meta/steps"])):
         sut()
         check_against_snapshot(sut, s, step)

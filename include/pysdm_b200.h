@@ -158,6 +158,47 @@ int pysdm_b200_volume_of_water_mass(double *volume, const double *mass, int64_t 
 int pysdm_b200_mass_of_water_volume(double *mass, const double *volume, int64_t n,
                                     double rho_w, void *stream);
 
+/* largest cell population max_c(cell_start[c+1]-cell_start[c]) -> *host_result */
+int pysdm_b200_max_cell_size(const int64_t *cell_start, int64_t n_cell, int64_t *host_result,
+                             int64_t *dev_scratch, void *stream);
+
+/* ---- fused collision step --------------------------------------------------------- */
+/* One launch = one Collision.step() (PySDM/dynamics/collisions/collision.py:196-234) of a
+ * `Coalescence` dynamic with the "local" croupier on a population whose idx is sorted
+ * by cell: shuffle_local, find_pairs, sort_within_pair_by_attr(multiplicity), collision
+ * kernel, max_pair, normalize, /= substeps, compute_gamma, collision_coalescence --
+ * with bit-identical results in every API-visible array.  Cells larger than
+ * pysdm_b200_fused_max_cell_size() are refused (cudaErrorInvalidConfiguration): the
+ * caller then runs the method-level entry points above. */
+typedef struct pysdm_b200_fused_args {
+    const int64_t *idx_in;      /* [n_sd] sorted by cell; working length `length` */
+    int64_t *idx_out;           /* [n_sd] permuted order out (caller swaps the buffers) */
+    const int64_t *cell_start;  /* [n_cell + 1] */
+    const int64_t *cell_idx;    /* [n_cell] */
+    const int64_t *cell_id;     /* [n_sd] */
+    int64_t *multiplicity;      /* [n_sd] */
+    double *attributes;         /* [n_attr, n_sd] extensive attributes, row-major */
+    const double *u01;          /* [>= length] uniforms for the shuffle; NULL = Philox */
+    const double *rand;         /* [n_sd / 2] uniforms for gamma; NULL = Philox */
+    uint8_t *is_first_in_pair;  /* [n_sd] */
+    double *gamma;              /* [n_sd / 2] */
+    double *norm_factor;        /* [n_cell] */
+    int64_t *collision_rate, *collision_rate_deficit, *coalescence_rate; /* [n_cell] */
+    int64_t *healthy;           /* [1] */
+    int64_t *status;            /* [1] set != 0 if a batch of cells did not fit */
+    int64_t length, n_sd, n_cell, n_attr, mass_row;
+    int64_t cells_per_batch;    /* filled in by the launcher */
+    uint64_t seed, call_u01, call_rand; /* Philox stream: Random(seed), call numbers */
+    double timestep, dv, rho_w, substeps;
+    double kernel_a, kernel_b;  /* Golovin: b; ConstantK: a; Linear: a, b */
+    int32_t kernel;             /* 0 Golovin, 1 ConstantK, 2 Linear */
+    int32_t reserved;
+    int64_t max_cell_size;      /* upper bound of cell_start[c+1]-cell_start[c] (host hint) */
+} pysdm_b200_fused_args;
+
+int64_t pysdm_b200_fused_max_cell_size(void);
+int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *host_args, void *stream);
+
 /* PYSDM_B200_H_END_OF_METHOD_LEVEL -- fused step and later additions follow */
 
 #ifdef __cplusplus

@@ -50,8 +50,27 @@ SIGNATURES = {
     "pysdm_b200_philox_raw": (INT, (P, U32, U32, U32, U32, U32, U32, P)),
     "pysdm_b200_volume_of_water_mass": (INT, (P, P, I64, F64, P)),
     "pysdm_b200_mass_of_water_volume": (INT, (P, P, I64, F64, P)),
+    "pysdm_b200_max_cell_size": (INT, (P, I64, P, P, P)),
+    "pysdm_b200_fused_max_cell_size": (I64, ()),
+    "pysdm_b200_fused_collision_step": (INT, (P, P)),
 }
 
+
+
+class FusedArgs(ctypes.Structure):
+    """mirror of pysdm_b200_fused_args (include/pysdm_b200.h)"""
+    _fields_ = ([(n, P) for n in (
+        "idx_in", "idx_out", "cell_start", "cell_idx", "cell_id", "multiplicity", "attributes",
+        "u01", "rand", "is_first_in_pair", "gamma", "norm_factor", "collision_rate",
+        "collision_rate_deficit", "coalescence_rate", "healthy", "status")]
+        + [(n, I64) for n in ("length", "n_sd", "n_cell", "n_attr", "mass_row",
+                              "cells_per_batch")]
+        + [(n, U64) for n in ("seed", "call_u01", "call_rand")]
+        + [(n, F64) for n in ("timestep", "dv", "rho_w", "substeps", "kernel_a", "kernel_b")]
+        + [("kernel", ctypes.c_int32), ("reserved", ctypes.c_int32), ("max_cell_size", I64)])
+
+
+KERNELS = {"Golovin": 0, "ConstantK": 1, "Linear": 2}
 EW = {"add": 0, "sub": 1, "mul": 2, "div": 3, "div_if_not_zero": 4, "pow": 5, "axpy": 6,
       "floor": 7, "exp": 8, "abs": 9, "mod": 10}
 PAIR_OPS = {"distance": 0, "max": 1, "min": 2, "sum": 3, "multiply": 4}

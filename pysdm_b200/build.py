@@ -8,6 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libpysdm_b200.so")
+INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 SOURCES = ("index.cu", "pairs.cu", "storage_ops.cu", "physics.cu", "fused.cu")
 NVCC_FLAGS = (
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -34,13 +35,14 @@ def is_stale():
         return True
     t = os.path.getmtime(SO)
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
+    deps.append(os.path.join(INCLUDE, "pysdm_b200.h"))
     return any(os.path.getmtime(d) > t for d in deps)
 
 
 def build_extension(force=False, verbose=False):
     if not force and not is_stale():
         return SO
-    cmd = [nvcc_path(), *NVCC_FLAGS, "-I", CSRC, "-o", SO, *sources()]
+    cmd = [nvcc_path(), *NVCC_FLAGS, "-I", CSRC, "-I", INCLUDE, "-o", SO, *sources()]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))

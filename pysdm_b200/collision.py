@@ -1,0 +1,298 @@
+"""Device-resident SDM collision step: state in HBM, one object = the collision part of a
+`Particulator` (the `Coalescence` dynamic + the `ParticleAttributes` bookkeeping it drives).
+
+It follows the reference's control flow call by call
+  Collision.__call__/step/compute_gamma     PySDM/dynamics/collisions/collision.py:174-290
+  ParticleAttributes (sort/permutation/sanitize/working length)   PySDM/impl/particle_attributes.py:42-111
+  RandomGeneratorOptimizer                  PySDM/dynamics/impl/random_generator_optimizer.py:19-48
+  Particulator.collision_coalescence_breakup   PySDM/particulator.py:157-213
+so it can be used stand-alone (bench.py, tests on a box without PySDM) with results
+identical to `Builder(...).build(...)` + `particulator.run()` under the reference backend.
+
+Two execution modes over the same state:
+  * method level -- one CUDA kernel (group) per reference backend method (pysdm_b200.methods);
+  * fused        -- one launch per step (csrc/fused.cu) for non-adaptive Coalescence with the
+                    "local" croupier and a Golovin / ConstantK / Linear kernel, when every cell
+                    fits a CTA batch.  Selected automatically; bit-identical to the first mode.
+There is no CPU path.
+"""
+
+import math
+
+import numpy as np
+import torch
+
+from . import methods as m
+from .random import HostReplayRandom, Random
+
+
+class Golovin:
+    """collision_kernels/golovin.py:14-16"""
+    fused = "Golovin"
+
+    def __init__(self, b):
+        self.a, self.b = 0.0, b
+
+    def __call__(self, sim, output, flag):
+        m.pair_op("sum", output, sim.volume(), flag, sim.idx, sim.length)
+        m.elementwise("mul", output, output, None, self.b)
+
+
+class ConstantK:
+    """collision_kernels/constantK.py"""
+    fused = "ConstantK"
+
+    def __init__(self, a):
+        self.a, self.b = a, 0.0
+
+    def __call__(self, sim, output, flag):
+        output.fill_(self.a)
+
+
+class Linear:
+    """collision_kernels/linear.py"""
+    fused = "Linear"
+
+    def __init__(self, a, b):
+        self.a, self.b = a, b
+
+    def __call__(self, sim, output, flag):
+        m.pair_op("sum", output, sim.volume(), flag, sim.idx, sim.length)
+        m.elementwise("mul", output, output, None, self.b)
+        m.elementwise("add", output, output, None, self.a)
+
+
+class DeviceCollision:  # pylint: disable=too-many-instance-attributes
+    """`Coalescence(collision_kernel=kernel, ...)` on a Box or a mesh of `n_cell` cells"""
+
+    def __init__(self, *, multiplicity, water_mass, cell_id=None, n_cell=1, dt, dv, kernel, seed,
+                 adaptive=False, substeps=1, dt_coal_range=(0.1, 100.0), croupier="local",
+                 optimized_random=False, rho_w=1000.0, extra_attributes=None, rnd=None,
+                 host_rng=False, fused="auto", device="cuda"):
+        assert substeps == 1 or adaptive is False
+        if not torch.cuda.is_available():
+            raise RuntimeError("pysdm_b200 needs a CUDA device (no CPU fallback)")
+        dev = torch.device(device)
+        self.device = dev
+        self.n_sd = len(multiplicity)
+        self.n_cell = int(n_cell)
+        self.dt, self.dv, self.kernel, self.rho_w = dt, dv, kernel, rho_w
+        self.adaptive, self.substeps, self.croupier = adaptive, substeps, croupier
+        self.dt_coal_range = (dt_coal_range[0], min(dt_coal_range[1], dt))
+
+        def up(array, dtype):
+            if isinstance(array, torch.Tensor):
+                return array.to(device=dev, dtype=dtype).contiguous().clone()
+            return torch.from_numpy(np.ascontiguousarray(array)).to(device=dev, dtype=dtype)
+
+        def full(n, value, dtype):
+            return torch.full((n,), value, dtype=dtype, device=dev)
+
+        i64, f64 = torch.int64, torch.float64
+        self.multiplicity = up(multiplicity, i64)
+        rows = [water_mass] + list(extra_attributes or [])
+        self.attributes = torch.stack([up(r, f64) for r in rows]).contiguous()
+        self.cell_id = full(self.n_sd, 0, i64) if cell_id is None else up(cell_id, i64)
+        # ParticleAttributes.__init__ (impl/particle_attributes.py:24-40)
+        self.idx = torch.arange(self.n_sd, dtype=i64, device=dev)
+        self.tmp_idx = full(self.n_sd, -1, i64)
+        self.length = self.n_sd
+        self.valid_n_sd = self.n_sd
+        self.cell_idx = torch.arange(self.n_cell, dtype=i64, device=dev)
+        self.cell_start = full(self.n_cell + 1, 0, i64)
+        self.sorted = False
+        self.max_cell = None
+        self.healthy = full(1, 1, i64)
+        # Collision.register (collision.py:101-172)
+        n_pairs = self.n_sd // 2
+        nan = float("nan")
+        self.kernel_temp = full(n_pairs, nan, f64)
+        self.gamma = full(n_pairs, nan, f64)
+        self.flag = torch.ones(self.n_sd, dtype=torch.bool, device=dev)
+        self.norm_factor = full(self.n_cell, nan, f64)
+        self.dt_left = full(self.n_cell, nan, f64)
+        self.stats_n_substep = full(self.n_cell, 0 if adaptive else substeps, i64)
+        self.stats_dt_min = full(self.n_cell, nan, f64)
+        self.collision_rate = full(self.n_cell, 0, i64)
+        self.collision_rate_deficit = full(self.n_cell, 0, i64)
+        self.coalescence_rate = full(self.n_cell, 0, i64)
+        self.status = full(1, 0, i64)
+        # RandomGeneratorOptimizer.register
+        self.optimized_random = optimized_random
+        shift = math.ceil(dt / dt_coal_range[0]) if optimized_random else 0
+        self.pairs_rand = full(self.n_sd + shift, nan, f64)
+        self.rand = full(n_pairs, nan, f64)
+        if rnd is None:
+            rnd = (HostReplayRandom if host_rng else Random)(self.n_sd + shift, seed)
+        self.rnd = rnd
+        self.substep = 0
+        self._volume = full(self.n_sd, nan, f64)
+        self.dt_min_warning = False
+        self.fused = fused
+        self.n_fused_steps = 0
+        self.n_launches = 0  # CUDA launches issued through the C-ABI (entry-point calls)
+        self._healthy_host = torch.ones(1, dtype=i64).pin_memory()
+        # Builder.build: zero multiplicities are removed up front
+        if bool((self.multiplicity == 0).any().item()):
+            self.healthy.zero_()
+            self.sanitize()
+
+    # ---- attributes -------------------------------------------------------------------
+    def volume(self):
+        m.volume_of_water_mass(self._volume, self.attributes[0], self.rho_w)
+        return self._volume
+
+    def sort_by_cell_id(self):
+        m.counting_sort_by_cell_id(self.tmp_idx, self.idx, self.cell_id, self.cell_idx,
+                                   self.length, self.cell_start)
+        self.idx, self.tmp_idx = self.tmp_idx, self.idx
+        self.sorted = True
+        self.max_cell = None
+
+    def get_cell_start(self):
+        if not self.sorted:
+            self.sort_by_cell_id()
+        return self.cell_start
+
+    def is_healthy(self):
+        self._healthy_host.copy_(self.healthy, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return bool(self._healthy_host[0])
+
+    def sanitize(self):
+        if not self.is_healthy():
+            self.length = self.valid_n_sd
+            self.length = m.remove_zero_n_or_flagged(self.multiplicity, self.idx, self.length)
+            self.valid_n_sd = self.length
+            self.healthy.fill_(1)
+            self.sorted = False
+
+    def permutation(self, u01, local):
+        if local:
+            cell_start = self.get_cell_start()
+            m.shuffle_local(self.idx, u01, cell_start, self.length)
+        else:
+            m.shuffle_global(self.idx, self.length, u01)
+            self.sorted = False
+
+    # ---- random numbers -----------------------------------------------------------------
+    def get_random_arrays(self):
+        if self.optimized_random:
+            shift = self.substep
+            if self.substep == 0:
+                self.rnd(_View(self.pairs_rand))
+                self.rnd(_View(self.rand))
+        else:
+            shift = 0
+            self.rnd(_View(self.pairs_rand))
+            self.rnd(_View(self.rand))
+        self.substep += 1
+        return self.pairs_rand[shift:self.n_sd + shift], self.rand
+
+    # ---- the dynamic ---------------------------------------------------------------------
+    def __call__(self):
+        if not self.adaptive:
+            for _ in range(self.substeps):
+                self.step()
+        else:
+            self.dt_left.fill_(self.dt)
+            while self.length != 0:
+                m.sort_by_key(self.cell_idx, self.dt_left)
+                self.step()
+                end = m.adaptive_sdm_end(self.dt_left, self.get_cell_start())
+                assert end <= self.length
+                self.length = end
+            self.length = self.valid_n_sd
+            m.identity_index(self.cell_idx)
+            self.sort_by_cell_id()
+        self.substep = 0
+
+    def run(self, steps):
+        for _ in range(steps):
+            self()
+
+    def _fused_ok(self):
+        if self.fused is False or self.adaptive or self.croupier != "local":
+            return False
+        if getattr(self.kernel, "fused", None) is None or self.optimized_random:
+            return False
+        self.get_cell_start()
+        if self.max_cell is None:
+            self.max_cell = m.max_cell_size(self.cell_start)
+        ok = self.max_cell <= m.fused_max_cell_size()
+        if not ok and self.fused is True:
+            raise RuntimeError(f"fused step refused: a cell holds {self.max_cell} super-droplets")
+        return ok
+
+    def step(self):
+        if self._fused_ok():
+            self.step_fused()
+        else:
+            self.step_methods()
+        self.sanitize()
+
+    def step_fused(self):
+        """one launch: csrc/fused.cu"""
+        kw = {}
+        if isinstance(self.rnd, Random):  # uniforms generated in-kernel from the same stream
+            kw = {"seed": self.rnd.seed, "call_u01": self.rnd.call, "call_rand": self.rnd.call + 1}
+            self.rnd.call += 2
+        else:
+            pairs_rand, rand = self.get_random_arrays()
+            kw = {"u01": pairs_rand, "rand": rand}
+        err = m.fused_collision_step(
+            idx_in=self.idx, idx_out=self.tmp_idx, cell_start=self.cell_start,
+            cell_idx=self.cell_idx, cell_id_=self.cell_id, multiplicity=self.multiplicity,
+            attributes=self.attributes, is_first_in_pair=self.flag, gamma=self.gamma,
+            norm_factor=self.norm_factor, collision_rate=self.collision_rate,
+            collision_rate_deficit=self.collision_rate_deficit,
+            coalescence_rate=self.coalescence_rate, healthy=self.healthy, status=self.status,
+            length=self.length, max_cell=self.max_cell, kernel=self.kernel.fused,
+            kernel_a=self.kernel.a, kernel_b=self.kernel.b, timestep=self.dt, dv=self.dv,
+            rho_w=self.rho_w, substeps=self.substeps, **kw)
+        m.check(err, "fused_collision_step")
+        # positions beyond the working length keep their content (flagged SDs)
+        if self.length < self.n_sd:
+            self.tmp_idx[self.length:] = self.idx[self.length:]
+        self.idx, self.tmp_idx = self.tmp_idx, self.idx
+        self.n_fused_steps += 1
+        self.n_launches += 1
+
+    def step_methods(self):
+        """the reference's sequence of backend calls, one kernel (group) each"""
+        pairs_rand, rand = self.get_random_arrays()
+        self.permutation(pairs_rand, self.croupier == "local")
+        cell_start = self.get_cell_start()
+        m.find_pairs(cell_start, self.flag, self.cell_id, self.cell_idx, self.idx, self.length)
+        m.sort_within_pair_by_attr(self.idx, self.length, self.flag, self.multiplicity)
+        prob = self.gamma
+        self.kernel(self, self.kernel_temp, self.flag)
+        m.pair_op("max", prob, self.multiplicity, self.flag, self.idx, self.length)
+        m.elementwise("mul", prob, prob, self.kernel_temp)
+        m.normalize(prob, self.cell_id, self.cell_idx, self.get_cell_start(), self.norm_factor,
+                    self.dt, self.dv)
+        if self.adaptive:
+            m.scale_prob_for_adaptive_sdm_gamma(prob, self.idx, self.length, self.multiplicity,
+                                                self.cell_id, self.dt_left, self.dt,
+                                                self.dt_coal_range, self.flag,
+                                                self.stats_n_substep, self.stats_dt_min)
+        else:
+            m.elementwise("div", prob, prob, None, self.substeps)
+        m.compute_gamma(prob, rand, self.idx, self.length, self.multiplicity, self.cell_id,
+                        self.collision_rate_deficit, self.collision_rate, self.flag, self.gamma)
+        m.collision_coalescence(self.multiplicity, self.idx, self.length, self.attributes,
+                                self.gamma, self.healthy, self.cell_id, self.coalescence_rate,
+                                self.flag)
+        self.n_launches += 14
+
+    # ---- host views for tests -------------------------------------------------------------
+    def host(self, name):
+        return getattr(self, name).cpu().numpy()
+
+
+class _View:  # pylint: disable=too-few-public-methods
+    """the minimal Storage face (`.data`, `.shape`) the Random classes fill"""
+
+    def __init__(self, tensor):
+        self.data = tensor
+        self.shape = tuple(tensor.shape)

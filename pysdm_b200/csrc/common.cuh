@@ -14,6 +14,7 @@ typedef int32_t i32;
 typedef uint64_t u64;
 typedef uint32_t u32;
 typedef uint8_t u8;
+typedef uint16_t u16;
 
 #define PYSDM_EXPORT extern "C" __attribute__((visibility("default")))
 

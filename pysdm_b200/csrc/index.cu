@@ -471,3 +471,43 @@ PYSDM_EXPORT int pysdm_b200_cell_id(i64 *cell_id, const i64 *cell_origin, const 
                                                                     n_dims, n_sd);
     return LAUNCH_CHECK();
 }
+
+// ---------------------------------------------------------------------------------
+// largest cell population: max_c (cell_start[c+1] - cell_start[c]) -> *host_result
+// (host-side dispatch between the fused step and the method-level kernels)
+// ---------------------------------------------------------------------------------
+__global__ void k_max_cell_size(const i64 *__restrict__ cell_start, i64 n_cell,
+                                unsigned long long *__restrict__ result)
+{
+    i64 m = 0;
+    for (i64 c = (i64)blockIdx.x * blockDim.x + threadIdx.x; c < n_cell;
+         c += (i64)gridDim.x * blockDim.x) {
+        i64 n = cell_start[c + 1] - cell_start[c];
+        m = n > m ? n : m;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        i64 t = __shfl_xor_sync(0xffffffffu, m, o);
+        m = t > m ? t : m;
+    }
+    if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(result, (unsigned long long)m);
+}
+
+PYSDM_EXPORT int pysdm_b200_max_cell_size(const i64 *cell_start, i64 n_cell, i64 *host_result,
+                                          i64 *dev_scratch, void *stream)
+{
+    cudaStream_t st = (cudaStream_t)stream;
+    int err = (int)cudaMemsetAsync(dev_scratch, 0, sizeof(i64), st);
+    if (err) return err;
+    if (n_cell > 0) {
+        int g = grid_for(n_cell);
+        if (g > 1184) g = 1184;
+        k_max_cell_size<<<g, kThreads, 0, st>>>(cell_start, n_cell,
+                                                (unsigned long long *)dev_scratch);
+        err = LAUNCH_CHECK();
+        if (err) return err;
+    }
+    err = (int)cudaMemcpyAsync(host_result, dev_scratch, sizeof(i64), cudaMemcpyDeviceToHost, st);
+    if (err) return err;
+    return (int)cudaStreamSynchronize(st);
+}

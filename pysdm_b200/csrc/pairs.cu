@@ -3,6 +3,7 @@
 // scale_prob_for_adaptive_sdm_gamma, adaptive_sdm_end, compute_gamma,
 // collision_coalescence(_breakup).  One launch per reference backend method
 // (drop-in granularity); the fused step lives in fused.cu and shares sdm_device.cuh.
+#include "pysdm_b200.h"
 #include "sdm_device.cuh"
 
 // ---------------------------------------------------------------------------------

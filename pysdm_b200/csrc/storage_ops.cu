@@ -3,6 +3,7 @@
 // (Philox4x32-10, counter based).  Reference semantics:
 //   impl_numba/storage.py:54-213 + storage_impl.py:11-83 (operators),
 //   impl_numba/random.py:9-19 (Random fills a Storage with uniforms in [0,1)).
+#include "pysdm_b200.h"
 #include <math.h>
 
 #include "primitives.cuh"
@@ -148,38 +149,7 @@ PYSDM_EXPORT int pysdm_b200_minmax_i64(const i64 *in, i64 n, int is_max, i64 *ho
                   : reduce_impl<i64, false>(in, n, host_result, scratch, (cudaStream_t)stream);
 }
 
-// ---- Philox4x32-10 -----------------------------------------------------------------
-// Element e of call number `call` under `seed` is a pure function of (seed, call, e):
-// counter = (e/2 lo, e/2 hi, call lo, call hi), key = (seed lo, seed hi); one Philox
-// block yields two doubles (53 random bits each, u = (x >> 11) * 2^-53 in [0, 1)).
-// Independent of launch geometry, so any kernel can regenerate element e in place.
-__device__ __forceinline__ void philox4x32_10(u32 c0, u32 c1, u32 c2, u32 c3, u32 k0, u32 k1,
-                                              u32 out[4])
-{
-    const u32 M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
-#pragma unroll
-    for (int r = 0; r < 10; ++r) {
-        u32 hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
-        u32 hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
-        u32 n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
-        c0 = n0;
-        c1 = n1;
-        c2 = n2;
-        c3 = n3;
-        k0 += W0;
-        k1 += W1;
-    }
-    out[0] = c0;
-    out[1] = c1;
-    out[2] = c2;
-    out[3] = c3;
-}
-
-__device__ __forceinline__ double u01_from_words(u32 hi, u32 lo)
-{
-    u64 x = ((u64)hi << 32) | (u64)lo;
-    return (double)(x >> 11) * 0x1.0p-53;
-}
+#include "philox.cuh"
 
 __global__ void k_philox_uniform(double *__restrict__ out, i64 n, u64 seed, u64 call)
 {

@@ -210,3 +210,55 @@ def scale_prob_for_adaptive_sdm_gamma(prob, idx, length, multiplicity, cell_id_,
 
 def host_ptr(tensor):
     return ctypes.c_void_p(tensor.data_ptr())
+
+
+# ---- Storage arithmetic ------------------------------------------------------------------
+def elementwise(op, out, a=None, b=None, scalar=0.0):
+    """out = a <op> (b or scalar); see include/pysdm_b200.h for the op table"""
+    check(_lib.load().pysdm_b200_elementwise(_lib.EW[op], _pf(out), _pf(a), _pf(b), float(scalar),
+                                             out.numel(), _stream()), op)
+
+
+def philox_uniform(out, seed, call):
+    check(_lib.load().pysdm_b200_philox_uniform(_pf(out), out.numel(), int(seed), int(call),
+                                                _stream()), "philox_uniform")
+
+
+def max_cell_size(cell_start):
+    """largest cell_start[c+1] - cell_start[c] (host int; synchronises)"""
+    box = WS.box()
+    scratch = WS.dev("max_cell", 64, cell_start.device)
+    check(_lib.load().pysdm_b200_max_cell_size(_pi(cell_start), cell_start.numel() - 1,
+                                               box.data_ptr(), _p(scratch), _stream()),
+          "max_cell_size")
+    return int(box[0])
+
+
+# ---- fused step ----------------------------------------------------------------------------
+def fused_max_cell_size():
+    return int(_lib.load().pysdm_b200_fused_max_cell_size())
+
+
+def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, multiplicity,
+                         attributes, is_first_in_pair, gamma, norm_factor, collision_rate,
+                         collision_rate_deficit, coalescence_rate, healthy, status, length,
+                         max_cell, kernel, kernel_a=0.0, kernel_b=0.0, timestep, dv, rho_w,
+                         substeps=1, mass_row=0, u01=None, rand=None, seed=0, call_u01=0,
+                         call_rand=0):
+    """one Collision.step() in one launch; returns the CUDA error code (9 = a cell is
+    larger than the fused path supports -> use the method-level functions)"""
+    n_attr, n_sd = attributes.shape
+    args = _lib.FusedArgs(
+        idx_in=_pi(idx_in), idx_out=_pi(idx_out), cell_start=_pi(cell_start),
+        cell_idx=_pi(cell_idx), cell_id=_pi(cell_id_), multiplicity=_pi(multiplicity),
+        attributes=_pf(attributes), u01=_pf(u01), rand=_pf(rand),
+        is_first_in_pair=_pb(is_first_in_pair), gamma=_pf(gamma), norm_factor=_pf(norm_factor),
+        collision_rate=_pi(collision_rate), collision_rate_deficit=_pi(collision_rate_deficit),
+        coalescence_rate=_pi(coalescence_rate), healthy=_pi(healthy), status=_pi(status),
+        length=int(length), n_sd=n_sd, n_cell=cell_start.numel() - 1, n_attr=n_attr,
+        mass_row=int(mass_row), cells_per_batch=0, seed=int(seed) & 0xFFFFFFFFFFFFFFFF,
+        call_u01=int(call_u01), call_rand=int(call_rand), timestep=float(timestep),
+        dv=float(dv), rho_w=float(rho_w), substeps=float(substeps), kernel_a=float(kernel_a),
+        kernel_b=float(kernel_b), kernel=_lib.KERNELS[kernel], reserved=0,
+        max_cell_size=int(max_cell))
+    return _lib.load().pysdm_b200_fused_collision_step(ctypes.byref(args), _stream())

@@ -1,0 +1,155 @@
+"""GPU: the device-resident collision step (pysdm_b200.collision.DeviceCollision), in its
+method-level and fused modes, against (a) the state snapshots the reference itself
+produced (tests/golden/scenario_*.npz) and (b) the CPU oracle on larger seeded inputs.
+Bit-exact: permutation, pair flags, gamma (sign of zero included), multiplicities,
+counters and -- for coalescence -- the attributes too."""
+
+import numpy as np
+import pytest
+
+from oracle.sdm_step import Golovin as OGolovin
+from oracle.sdm_step import OracleCollision
+
+from .golden_util import (GOLOVIN_B, SCENARIO_KW, SCENARIOS, assert_same_f64, load_scenario)
+
+pytestmark = pytest.mark.gpu
+
+
+def device_sim(**kw):
+    from pysdm_b200.collision import DeviceCollision  # pylint: disable=import-outside-toplevel
+
+    return DeviceCollision(**kw)
+
+
+def device_kernel(name="Golovin", **kw):
+    from pysdm_b200 import collision  # pylint: disable=import-outside-toplevel
+
+    return getattr(collision, name)(**kw)
+
+
+def compare_states(dev, ora, what):
+    assert dev.length == ora.length, f"{what}: length"
+    n = ora.length
+    np.testing.assert_array_equal(dev.host("idx")[:n], ora.idx[:n], f"{what}: idx")
+    np.testing.assert_array_equal(dev.host("flag")[:n], ora.flag[:n], f"{what}: flag")
+    np.testing.assert_array_equal(dev.host("multiplicity"), ora.multiplicity, f"{what}: n")
+    assert_same_f64(dev.host("attributes"), ora.attributes, f"{what}: attributes")
+    assert_same_f64(dev.host("gamma"), ora.gamma, f"{what}: gamma")
+    assert_same_f64(dev.host("norm_factor"), ora.norm_factor, f"{what}: norm_factor")
+    for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate", "stats_n_substep",
+              "cell_start"):
+        np.testing.assert_array_equal(dev.host(k), getattr(ora, k), f"{what}: {k}")
+    assert_same_f64(dev.host("stats_dt_min"), ora.stats_dt_min, f"{what}: stats_dt_min")
+
+
+@pytest.mark.parametrize("fused", ("auto", False))
+@pytest.mark.parametrize("name", SCENARIOS)
+def test_reference_scenarios(name, fused):
+    s = load_scenario(name)
+    kw = dict(SCENARIO_KW[name])
+    multi = "init/cell id" in s.files and int(s["meta/n_cell"]) > 1
+    sut = device_sim(
+        multiplicity=s["init/multiplicity"], water_mass=s["init/signed water mass"],
+        cell_id=s["init/cell id"] if multi else None, n_cell=int(s["meta/n_cell"]),
+        dt=float(s["meta/dt"]), dv=float(s["meta/dv"]), kernel=device_kernel(b=GOLOVIN_B),
+        seed=int(s["meta/seed"]), rho_w=float(s["meta/rho_w"]), host_rng=True, fused=fused, **kw)
+    for step in range(int(s["meta/steps"])):
+        sut()
+        p = f"step{step}/"
+        length = int(s[p + "length"])
+        assert sut.length == length, f"step {step}: length"
+        np.testing.assert_array_equal(sut.host("idx")[:length], s[p + "idx"][:length])
+        np.testing.assert_array_equal(sut.host("flag")[:length], s[p + "flag"][:length])
+        np.testing.assert_array_equal(sut.host("multiplicity"), s[p + "multiplicity"])
+        assert_same_f64(sut.host("attributes"), s[p + "attributes"], f"step {step} attributes")
+        assert_same_f64(sut.host("gamma"), s[p + "gamma"], f"step {step} gamma")
+        for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate",
+                  "stats_n_substep"):
+            np.testing.assert_array_equal(sut.host(k), s[p + k], f"step {step} {k}")
+    if fused == "auto" and name in ("golovin_local", "golovin_substeps", "golovin_box"):
+        assert sut.n_fused_steps > 0, "the fused kernel was expected to run"
+
+
+def ragged_population(seed, n_cell, mean, n_attr=1, max_mult=4):
+    rng = np.random.default_rng(seed)
+    sizes = rng.poisson(mean, n_cell)
+    sizes[rng.integers(0, n_cell, max(1, n_cell // 10))] = 0   # empty cells
+    sizes[rng.integers(0, n_cell, max(1, n_cell // 10))] = 1   # lonely SDs
+    sizes[rng.integers(0, n_cell, max(1, n_cell // 10))] = 3   # odd cells
+    cell_id = np.repeat(np.arange(n_cell), sizes)
+    n_sd = len(cell_id)
+    perm = rng.permutation(n_sd)  # SDs are NOT stored cell-contiguously
+    cell_id = cell_id[perm]
+    mult = rng.integers(1, max_mult + 1, n_sd).astype(np.int64)
+    mass = rng.exponential(1000 * 4 / 3 * np.pi * (30.531e-6) ** 3, n_sd)
+    extra = [rng.exponential(1e-18, n_sd) for _ in range(n_attr - 1)]
+    return {"multiplicity": mult, "water_mass": mass, "cell_id": cell_id, "n_cell": n_cell,
+            "extra_attributes": extra}
+
+
+CASES = {
+    "ragged_small_cells": dict(seed=1, n_cell=700, mean=14, n_attr=1, dv=2e-8, steps=6),
+    "ragged_128": dict(seed=2, n_cell=300, mean=128, n_attr=3, dv=4e-7, steps=5),
+    "big_cells": dict(seed=3, n_cell=5, mean=3000, n_attr=1, dv=2e-5, steps=3),
+    "substeps": dict(seed=4, n_cell=64, mean=40, n_attr=2, dv=1e-7, steps=4, substeps=3),
+    "one_cell": dict(seed=5, n_cell=1, mean=5000, n_attr=1, dv=1e-4, steps=3),
+}
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+@pytest.mark.parametrize("fused", (True, False))
+def test_against_oracle(case, fused):
+    c = dict(CASES[case])
+    steps, dv = c.pop("steps"), c.pop("dv")
+    substeps = c.pop("substeps", 1)
+    pop = ragged_population(**c)
+    if case == "one_cell":
+        pop["cell_id"] = np.zeros_like(pop["cell_id"])
+    common = dict(dt=1.0, dv=dv, seed=100 + c["seed"], substeps=substeps)
+    ora = OracleCollision(kernel=OGolovin(GOLOVIN_B), **pop, **common)
+    dev = device_sim(kernel=device_kernel(b=GOLOVIN_B), host_rng=True, fused=fused, **pop,
+                     **common)
+    for step in range(steps):
+        ora()
+        dev()
+        compare_states(dev, ora, f"{case} step {step}")
+    assert ora.coalescence_rate.sum() > 0, "test population never collided"
+    if fused:
+        assert dev.n_fused_steps == steps * substeps
+
+
+@pytest.mark.parametrize("kernel", ("ConstantK", "Linear"))
+def test_fused_equals_methods_other_kernels(kernel):
+    """fused vs method-level CUDA path (itself pinned by the tests above)"""
+    pop = ragged_population(seed=7, n_cell=200, mean=60, n_attr=2)
+    kw = {"ConstantK": {"a": 3e-4}, "Linear": {"a": 1e-4, "b": GOLOVIN_B}}[kernel]
+    sims = [device_sim(kernel=device_kernel(kernel, **kw), dt=1.0, dv=1e-3, seed=3, host_rng=True,
+                       fused=f, **pop) for f in (True, False)]
+    for step in range(4):
+        for s in sims:
+            s()
+        compare_states(sims[0], _Host(sims[1]), f"{kernel} step {step}")
+    assert sims[0].host("coalescence_rate").sum() > 0
+
+
+def test_fused_philox_equals_methods_philox():
+    """in-kernel Philox uniforms == the Random kernel's stream consumed by the method path"""
+    pop = ragged_population(seed=8, n_cell=500, mean=100, n_attr=1)
+    sims = [device_sim(kernel=device_kernel(b=GOLOVIN_B), dt=1.0, dv=2e-7, seed=11, fused=f, **pop)
+            for f in (True, False)]
+    for step in range(5):
+        for s in sims:
+            s()
+        compare_states(sims[0], _Host(sims[1]), f"philox step {step}")
+    assert sims[0].host("coalescence_rate").sum() > 0
+
+
+class _Host:  # pylint: disable=too-few-public-methods
+    """numpy face of a DeviceCollision, shaped like OracleCollision for compare_states"""
+
+    def __init__(self, sim):
+        self.sim = sim
+        self.length = sim.length
+
+    def __getattr__(self, name):
+        return self.sim.host(name)

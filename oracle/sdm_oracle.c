@@ -31,6 +31,16 @@ typedef uint8_t u8;
 
 #define ORACLE_API __attribute__((visibility("default")))
 
+/* thread control for the timed CPU baseline (bench.py sweeps the thread count) */
+#ifdef _OPENMP
+#include <omp.h>
+ORACLE_API void oracle_set_num_threads(int n) { omp_set_num_threads(n); }
+ORACLE_API int oracle_get_max_threads(void) { return omp_get_max_threads(); }
+#else
+ORACLE_API void oracle_set_num_threads(int n) { (void)n; }
+ORACLE_API int oracle_get_max_threads(void) { return 1; }
+#endif
+
 /* ---- pair_indices: methods/collisions_methods.py:16-35 ------------------ */
 static inline int pair_indices(i64 i, const i64 *idx, const u8 *is_first_in_pair,
                                const double *prob_like, i64 *j, i64 *k)

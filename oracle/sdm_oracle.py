@@ -43,6 +43,14 @@ def lib():
     return _lib
 
 
+def set_num_threads(n):
+    lib().oracle_set_num_threads(ctypes.c_int(int(n)))
+
+
+def get_max_threads():
+    return int(lib().oracle_get_max_threads())
+
+
 def _p(a, dtype=None):
     """pointer to a C-contiguous numpy array (checked, never copied)"""
     assert isinstance(a, np.ndarray), type(a)

@@ -101,6 +101,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.cell_idx = torch.arange(self.n_cell, dtype=i64, device=dev)
         self.cell_start = full(self.n_cell + 1, 0, i64)
         self.sorted = False
+        self.sorted_length = 0
         self.max_cell = None
         self.healthy = full(1, 1, i64)
         # Collision.register (collision.py:101-172)
@@ -147,6 +148,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
                                    self.length, self.cell_start)
         self.idx, self.tmp_idx = self.tmp_idx, self.idx
         self.sorted = True
+        self.sorted_length = self.length  # = cell_start[-1], kept on the host
         self.max_cell = None
 
     def get_cell_start(self):
@@ -170,7 +172,8 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
     def permutation(self, u01, local):
         if local:
             cell_start = self.get_cell_start()
-            m.shuffle_local(self.idx, u01, cell_start, self.length)
+            # the reference walks every cell of cell_start, also beyond a cut working length
+            m.shuffle_local(self.idx, u01, cell_start, self.sorted_length)
         else:
             m.shuffle_global(self.idx, self.length, u01)
             self.sorted = False

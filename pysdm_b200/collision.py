@@ -259,7 +259,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             self.tmp_idx[self.length:] = self.idx[self.length:]
         self.idx, self.tmp_idx = self.tmp_idx, self.idx
         self.n_fused_steps += 1
-        self.n_launches += 1
+        self.n_launches += 2  # norm_factor pre-pass + the fused step
 
     def step_methods(self):
         """the reference's sequence of backend calls, one kernel (group) each"""

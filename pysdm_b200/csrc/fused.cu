@@ -18,25 +18,74 @@
 // attributes, norm_factor, the per-cell rate counters and the `healthy` flag -- bit
 // for bit what the method-level kernels (and the reference) produce.
 //
-// Data movement (DESIGN.md "fused step"): a CTA owns a batch of consecutive cells whose
-// SDs occupy one contiguous range of positions.  The range of `idx` and of the uniforms
-// is streamed in with 16-byte loads and staged in shared memory as 32-bit SD numbers +
-// 16-bit swap targets; one thread per cell replays the cell's swap chain in shared
-// memory; then one thread per pair slot gathers multiplicity / mass (the only random
-// accesses, confined to the cell's own SDs), evaluates probability and gamma and
-// scatters the updates.  Nothing is written to HBM between those stages.
+// Data movement (DESIGN.md "fused step"): a GROUP of threads -- one warp when every cell
+// holds <= kWarpPos super-droplets, else a whole CTA -- owns a batch of consecutive cells
+// whose SDs occupy one contiguous range of positions.  The range of `idx` and of the
+// uniforms is streamed in with 16-byte loads and staged in shared memory as 32-bit SD
+// numbers + 16-bit swap targets; one lane per cell replays the cell's swap chain in shared
+// memory; then each lane handles two pair slots: gathers multiplicity / mass (the only
+// random accesses, confined to the cell's own SDs), evaluates probability and gamma and
+// scatters the updates.  Nothing is written to HBM between the stages, warps of the
+// warp-group variant never wait for each other.
+//
+// Instruction diet (ncu, profiles/): the step is bound by instruction issue and by the
+// conversion/transcendental pipe (XU) long before HBM unless 64-bit int<->fp conversions,
+// fp64 divisions and ceil() are kept out of the per-SD path; see the helpers below --
+// each is exact (bit-identical to the plain expression), with a guarded slow path.
 #include "philox.cuh"
 #include "pysdm_b200.h"
 #include "sdm_device.cuh"
-
-constexpr int kFusedThreads = 256;
-constexpr int kPosMax = 8192;   // positions (SDs) per batch
-constexpr int kCellMax = 256;   // cells per batch (one chain thread per cell)
 
 // C-ABI argument block: include/pysdm_b200.h (mirrored by ctypes in pysdm_b200/_lib.py)
 typedef pysdm_b200_fused_args FusedArgs;
 
 enum { KERNEL_GOLOVIN = 0, KERNEL_CONSTANT_K = 1, KERNEL_LINEAR = 2 };
+
+constexpr int kFusedThreads = 256;
+constexpr int kCtaPos = 8192, kCtaCells = 256;  // CTA group: positions / cells per batch
+constexpr int kWarpPos = 1024, kWarpCells = 32;  // warp group
+constexpr double kTwo52 = 4503599627370496.0;    // 2^52
+
+// ---- exact arithmetic helpers without XU-pipe instructions ---------------------------------
+// (double)n for 0 <= n < 2^52 by mantissa insertion; other values take the conversion
+__device__ __forceinline__ double i64_to_f64(i64 n)
+{
+    if ((u64)n < ((u64)1 << 52))
+        return __longlong_as_double((long long)(0x4330000000000000ull | (u64)n)) - kTwo52;
+    return (double)n;
+}
+// (i64)x (truncation) for integer-valued or fractional 0 <= x < 2^51; else the conversion
+__device__ __forceinline__ i64 f64_to_i64(double x)
+{
+    if (x >= 0.0 && x < 2251799813685248.0) {
+        double t = __dadd_rd(x, kTwo52);  // 2^52 + floor(x), exact
+        return (i64)((u64)__double_as_longlong(t) & 0x000FFFFFFFFFFFFFull);
+    }
+    return (i64)x;
+}
+// ceil(x) with the sign of zero of the IEEE result, for |x| < 2^51; else ceil()
+__device__ __forceinline__ double ceil_exact(double x)
+{
+    if (fabs(x) < 2251799813685248.0) {
+        const double c = 6755399441055744.0;  // 1.5 * 2^52: ulp = 1 around it
+        double r = __dadd_ru(x, c) - c;
+        if (r == 0.0) r = copysign(0.0, x);
+        return r;
+    }
+    return ceil(x);
+}
+// a / b given r = RN(1/b): Markstein's correction q' = fma(fma(-q, b, a), r, q) is the
+// correctly rounded quotient when q = RN(a*r) is faithful and nothing under/overflows
+// (`ok` = b is finite, normal, its significand not all ones; checked once on the host).
+__device__ __forceinline__ double div_by(double a, double b, double r, bool ok)
+{
+    const double m = fabs(a);
+    if (ok && m > 1e-280 && m < 1e280) {
+        const double q = a * r;
+        return fma(fma(-q, b, a), r, q);
+    }
+    return a / b;
+}
 
 // kernel_temp of a pair from the pair's volume sum (sum_pair result; 0 for non-pairs)
 template <int K>
@@ -47,289 +96,462 @@ __device__ __forceinline__ double kernel_temp_of(double vsum, double a, double b
     return vsum * b + a;                        // linear.py: sum; *= b; += a  (no FMA: -fmad=false)
 }
 
-__device__ __forceinline__ double philox_element(u64 seed, u64 call, i64 e)
+// ---- pre-pass: norm_factor per cell rank (normalize, collisions_methods.py:639-646) ---------
+__global__ void k_fused_norm_factor(const i64 *__restrict__ cell_start, i64 n_cell,
+                                    double *__restrict__ norm_factor, double timestep, double dv)
 {
-    u32 w[4];
-    u64 b = (u64)e >> 1;
-    philox4x32_10((u32)b, (u32)(b >> 32), (u32)call, (u32)(call >> 32), (u32)seed,
-                  (u32)(seed >> 32), w);
-    return (e & 1) ? u01_from_words(w[2], w[3]) : u01_from_words(w[0], w[1]);
+    i64 r = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < n_cell)
+        norm_factor[r] = sdm_norm_factor(cell_start[r + 1] - cell_start[r], timestep, dv);
 }
 
-// norm_factor of the cell with rank r (normalize, collisions_methods.py:639-646)
-__device__ __forceinline__ double norm_factor_of_rank(const i64 *__restrict__ cell_start, i64 r,
-                                                      double timestep, double dv)
+// ---- group geometry -----------------------------------------------------------------------
+template <bool kWarp>
+struct Geo {
+    static constexpr int kPos = kWarp ? kWarpPos : kCtaPos;        // positions per batch
+    static constexpr int kCells = kWarp ? kWarpCells : kCtaCells;  // cells per batch
+    static constexpr int kSize = kWarp ? 32 : kFusedThreads;       // threads per group
+    static constexpr int kGroups = kFusedThreads / kSize;          // groups per CTA
+    // shared-memory carve-up per group (bytes, 16-byte aligned sections)
+    // sd / jl are indexed through phys(): 2 pad elements per 64 positions, so that the chain
+    // lanes of equally sized cells (stride 128, 64, ...) fall into different banks
+    static constexpr int kPhys = kPos + 4 + 2 * ((kPos + 4) / 64 + 1);
+    static constexpr int kSd = (kPhys * 4 + 15) / 16 * 16;         // u32 SD numbers
+    static constexpr int kJl = (kPhys * 2 + 15) / 16 * 16;         // u16 swap targets
+    static constexpr int kCo = ((kPos + 4) * 1 + 15) / 16 * 16;    // u8 position -> cell
+    static constexpr int kCs = ((kCells + 1) * 4 + 15) / 16 * 16;  // i32 local cell starts
+    static constexpr int kFd = kCells * 16;                        // double S, len per cell
+    static constexpr int kCid = kCells * 8;                        // i64 cell id per cell
+    static constexpr int kBytes = kSd + kJl + kCo + kCs + kFd + kCid;
+    static constexpr int kSmem = kBytes * kGroups;
+};
+
+// skewed shared-memory index of local position lp (keeps even positions 8-byte aligned)
+__device__ __forceinline__ int phys(int lp) { return lp + 2 * (lp >> 6); }
+
+template <bool kWarp>
+__device__ __forceinline__ void group_sync()
 {
-    return sdm_norm_factor(cell_start[r + 1] - cell_start[r], timestep, dv);
+    if (kWarp)
+        __syncwarp();
+    else
+        __syncthreads();
 }
 
-// shared-memory carve-up (bytes, 16-byte aligned sections)
-constexpr int kSdBytes = ((kPosMax + 2) * 4 + 15) / 16 * 16;
-constexpr int kJlBytes = ((kPosMax + 2) * 2 + 15) / 16 * 16;
-constexpr int kCoBytes = ((kPosMax + 2) * 1 + 15) / 16 * 16;
-constexpr int kCsBytes = ((kCellMax + 1) * 4 + 15) / 16 * 16;
-constexpr int kCidBytes = kCellMax * 8;
-constexpr int kFusedSmem = kSdBytes + kJlBytes + kCoBytes + kCsBytes + kCidBytes;
+// per-cell int64 counter: per-lane RED when cells are many (no contention), warp-aggregated
+// when few (boxes); the aggregated form needs the whole warp converged at the call
+template <bool kAggregate>
+__device__ __forceinline__ void counter_add(i64 *counters, i64 cid, i64 value, bool active)
+{
+    if (kAggregate)
+        cell_counter_add(counters, cid, value, active);
+    else if (active && value != 0)
+        atomicAdd((unsigned long long *)&counters[cid], (unsigned long long)value);
+}
 
-template <int K, bool kPhilox>
+template <int K, bool kPhilox, bool kWarp, bool kAggregate>
 __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs a)
 {
-    extern __shared__ __align__(16) unsigned char smem[];
-    u32 *sd = reinterpret_cast<u32 *>(smem);
-    u16 *jl = reinterpret_cast<u16 *>(smem + kSdBytes);
-    u8 *cellof = smem + kSdBytes + kJlBytes;
-    i32 *cs = reinterpret_cast<i32 *>(smem + kSdBytes + kJlBytes + kCoBytes);
-    i64 *cidv = reinterpret_cast<i64 *>(smem + kSdBytes + kJlBytes + kCoBytes + kCsBytes);
-
+    typedef Geo<kWarp> G;
+    extern __shared__ __align__(16) unsigned char smem_all[];
     const int tid = threadIdx.x;
+    const int group = kWarp ? (tid >> 5) : 0;
+    const int gt = kWarp ? (tid & 31) : tid;  // thread number within the group
+    unsigned char *smem = smem_all + group * G::kBytes;
+    u32 *sd = reinterpret_cast<u32 *>(smem);
+    u16 *jl = reinterpret_cast<u16 *>(smem + G::kSd);
+    u8 *cellof = smem + G::kSd + G::kJl;
+    i32 *cs = reinterpret_cast<i32 *>(smem + G::kSd + G::kJl + G::kCo);
+    double *fd = reinterpret_cast<double *>(smem + G::kSd + G::kJl + G::kCo + G::kCs);
+    i64 *cidv = reinterpret_cast<i64 *>(smem + G::kSd + G::kJl + G::kCo + G::kCs + G::kFd);
+
     const i64 n_pairs_active = a.length / 2;
     // literal chain for a slot without a pair: max_pair -> 0; *= kernel_temp; normalize
     const double prob_nopair = 0.0 * kernel_temp_of<K>(0.0, a.kernel_a, a.kernel_b);
+    const bool unit_substeps = a.substeps == 1.0;
+    const double rho_rcp = 1.0 / a.rho_w;
+    const bool rho_ok = a.reserved != 0;  // host-checked precondition of div_by
 
     // ---- tail: pair slots beyond the working length keep `0 * norm_factor` ------------
     for (i64 d = n_pairs_active + (i64)blockIdx.x * kFusedThreads + tid; d < a.n_sd / 2;
-         d += (i64)gridDim.x * kFusedThreads) {
-        double nf = norm_factor_of_rank(a.cell_start, a.cell_idx[a.cell_id[d]], a.timestep, a.dv);
-        a.gamma[d] = prob_nopair * nf / a.substeps;
-    }
+         d += (i64)gridDim.x * kFusedThreads)
+        a.gamma[d] = prob_nopair * a.norm_factor[a.cell_idx[a.cell_id[d]]] / a.substeps;
 
-    const i64 c0 = (i64)blockIdx.x * a.cells_per_batch;
-    if (c0 >= a.n_cell) return;
+    const i64 batch = (i64)blockIdx.x * G::kGroups + group;
+    const i64 c0 = batch * a.cells_per_batch;
+    if (c0 >= a.n_cell) return;  // (warp groups: a whole warp leaves; no CTA barrier below)
     const i64 c1 = (c0 + a.cells_per_batch < a.n_cell) ? c0 + a.cells_per_batch : a.n_cell;
     const int ncb = (int)(c1 - c0);
     const i64 base = a.cell_start[c0], end = a.cell_start[c1];
-    if (end - base > kPosMax || ncb > kCellMax) {  // caller's max_cell_size hint was wrong
-        if (tid == 0) a.status[0] = 1;
+    if (end - base > G::kPos || ncb > G::kCells) {  // caller's max_cell_size hint was wrong
+        if (gt == 0) a.status[0] = 1;
         return;
     }
-    const i64 base_al = base & ~(i64)1;  // local position 0 <-> an even global position
+    const i64 base_al = base & ~(i64)3;  // local position 0 <-> a global multiple of 4
     const int lo = (int)(base - base_al);
     const int P = (int)(end - base_al);
 
     // ---- phase 0: cell boundaries ---------------------------------------------------------
-    for (int c = tid; c <= ncb; c += kFusedThreads) cs[c] = (i32)(a.cell_start[c0 + c] - base_al);
-    __syncthreads();
+    for (int c = gt; c <= ncb; c += G::kSize) cs[c] = (i32)(a.cell_start[c0 + c] - base_al);
+    group_sync<kWarp>();
 
-    // ---- phase 1: position -> cell map; per-cell norm_factor (API-visible) ----------------
-    {
-        const int warp = tid >> 5, lane = tid & 31;
-        for (int c = warp; c < ncb; c += kFusedThreads / 32) {
+    // ---- phase 1: position -> cell map, per-cell fp64 constants of the shuffle ------------
+    if (kWarp) {
+        for (int c = 0; c < ncb; ++c) {
             const int s = cs[c], e = cs[c + 1];
-            for (int lp = s + lane; lp < e; lp += 32) cellof[lp] = (u8)c;
+            for (int lp = s + gt; lp < e; lp += 32) cellof[lp] = (u8)c;
         }
-        for (int c = tid; c < ncb; c += kFusedThreads)
-            a.norm_factor[c0 + c] = sdm_norm_factor((i64)(cs[c + 1] - cs[c]), a.timestep, a.dv);
+    } else {
+        for (int c = tid >> 5; c < ncb; c += kFusedThreads / 32) {
+            const int s = cs[c], e = cs[c + 1];
+            for (int lp = s + (tid & 31); lp < e; lp += 32) cellof[lp] = (u8)c;
+        }
     }
-    __syncthreads();
+    for (int c = gt; c < ncb; c += G::kSize) {
+        fd[2 * c] = i64_to_f64(base_al + cs[c]);           // (double)cell_start[c]
+        fd[2 * c + 1] = i64_to_f64((i64)(cs[c + 1] - cs[c]));  // (double)(cell_end - cell_start)
+    }
+    group_sync<kWarp>();
+
+    // Work mapping of phases 2 and 4: an iteration covers 4 * kSize consecutive positions;
+    // thread gt owns two windows of two positions, (lp0, lp0 + 1) with
+    // lp0 = 4*kSize*it + 2*kSize*h + 2*gt, h = 0, 1  -> a warp touches 64 consecutive
+    // positions per window: 512-byte coalesced idx accesses, conflict-free 8-byte smem accesses.
+    const int n_iter = (P + 4 * G::kSize - 1) / (4 * G::kSize);
 
     // ---- phase 2: stream idx + uniforms in, stage SD numbers and swap targets -------------
     {
         const bool vec_idx = (((uintptr_t)a.idx_in) & 15) == 0;
         const bool vec_u = !kPhilox && (((uintptr_t)a.u01) & 15) == 0;
-#pragma unroll 4
-        for (int lp0 = 2 * tid; lp0 < P; lp0 += 2 * kFusedThreads) {
-            const i64 p0 = base_al + lp0;
-            const bool v0 = lp0 >= lo, v1 = lp0 + 1 < P;
-            i64 s0 = 0, s1 = 0;
-            double u0 = 0.0, u1 = 0.0;
-            if (v0 && v1 && vec_idx) {
-                longlong2 t = *reinterpret_cast<const longlong2 *>(a.idx_in + p0);
-                s0 = t.x;
-                s1 = t.y;
-            } else {
-                if (v0) s0 = a.idx_in[p0];
-                if (v1) s1 = a.idx_in[p0 + 1];
-            }
-            if (kPhilox) {
-                u32 w[4];
-                u64 b = (u64)p0 >> 1;
-                philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_u01, (u32)(a.call_u01 >> 32),
-                              (u32)a.seed, (u32)(a.seed >> 32), w);
-                u0 = u01_from_words(w[0], w[1]);
-                u1 = u01_from_words(w[2], w[3]);
-            } else if (v0 && v1 && vec_u) {
-                double2 t = *reinterpret_cast<const double2 *>(a.u01 + p0);
-                u0 = t.x;
-                u1 = t.y;
-            } else {
-                if (v0) u0 = a.u01[p0];
-                if (v1) u1 = a.u01[p0 + 1];
+        for (int it = 0; it < n_iter; ++it) {
+            i64 sv[2][2];
+            double uv[2][2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int lp0 = 4 * G::kSize * it + 2 * G::kSize * h + 2 * gt;
+                const i64 p0 = base_al + lp0;
+                const bool v0 = lp0 >= lo && lp0 < P, v1 = lp0 + 1 < P;
+                sv[h][0] = sv[h][1] = 0;
+                uv[h][0] = uv[h][1] = 0.0;
+                if (v0 && v1 && vec_idx) {
+                    const longlong2 t = *reinterpret_cast<const longlong2 *>(a.idx_in + p0);
+                    sv[h][0] = t.x;
+                    sv[h][1] = t.y;
+                } else {
+                    if (v0) sv[h][0] = a.idx_in[p0];
+                    if (v1) sv[h][1] = a.idx_in[p0 + 1];
+                }
+                if (kPhilox) {
+                    if (lp0 < P) {
+                        u32 w[4];
+                        const u64 b = (u64)p0 >> 1;  // Philox block = elements 2b, 2b + 1
+                        philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_u01,
+                                      (u32)(a.call_u01 >> 32), (u32)a.seed, (u32)(a.seed >> 32), w);
+                        uv[h][0] = u01_from_words(w[0], w[1]);
+                        uv[h][1] = u01_from_words(w[2], w[3]);
+                    }
+                } else if (v0 && v1 && vec_u) {
+                    const double2 t = *reinterpret_cast<const double2 *>(a.u01 + p0);
+                    uv[h][0] = t.x;
+                    uv[h][1] = t.y;
+                } else {
+                    if (v0) uv[h][0] = a.u01[p0];
+                    if (v1) uv[h][1] = a.u01[p0 + 1];
+                }
             }
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const int lp = lp0 + h;
-                if (h == 0 ? !v0 : !v1) continue;
-                const int c = cellof[lp];
-                const int s = cs[c], len = cs[c + 1] - s;
-                const i64 S = base_al + s;
-                // index_methods.py:40: j = int(cell_start[c] + u01[i] * (cell_end - cell_start))
-                i64 j = (i64)((double)S + (h == 0 ? u0 : u1) * (double)len);
-                if (j >= S + len) j = S + len - 1;  // fp round-up at huge S (see index.cu)
-                jl[lp] = (u16)(j - S);
-                sd[lp] = (u32)(h == 0 ? s0 : s1);
+                const int lp0 = 4 * G::kSize * it + 2 * G::kSize * h + 2 * gt;
+                u32 jrel[2] = {0, 0};
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const int lp = lp0 + q;
+                    if (lp < lo || lp >= P) continue;
+                    const int c = cellof[lp];
+                    const int s = cs[c], len = cs[c + 1] - s;
+                    // index_methods.py:40: j = int(cell_start[c] + u01[i] * (cell_end - cell_start));
+                    // 0 <= x < 2^33: floor by a round-down add, integer in the low mantissa bits
+                    const double x = fd[2 * c] + uv[h][q] * fd[2 * c + 1];
+                    const double t = __dadd_rd(x, kTwo52);
+                    i64 jr = (i64)((u64)__double_as_longlong(t) & 0x000FFFFFFFFFFFFFull) -
+                             (base_al + s);
+                    if (jr >= len) jr = len - 1;  // fp round-up at huge cell_start (see index.cu)
+                    jrel[q] = (u32)jr;
+                }
+                if (lp0 >= lo && lp0 + 1 < P) {
+                    const int ph = phys(lp0);
+                    *reinterpret_cast<uint2 *>(sd + ph) = make_uint2((u32)sv[h][0], (u32)sv[h][1]);
+                    *reinterpret_cast<u32 *>(jl + ph) = jrel[0] | (jrel[1] << 16);
+                } else {
+                    if (lp0 >= lo && lp0 < P) {
+                        sd[phys(lp0)] = (u32)sv[h][0];
+                        jl[phys(lp0)] = (u16)jrel[0];
+                    }
+                    if (lp0 + 1 >= lo && lp0 + 1 < P) {
+                        sd[phys(lp0 + 1)] = (u32)sv[h][1];
+                        jl[phys(lp0 + 1)] = (u16)jrel[1];
+                    }
+                }
             }
         }
     }
-    __syncthreads();
+    group_sync<kWarp>();
 
-    // ---- phase 3: one thread per cell replays the swap chain in shared memory -------------
-    for (int c = tid; c < ncb; c += kFusedThreads) {
+    // ---- phase 3: one lane per cell replays the swap chain in shared memory ---------------
+    for (int c = gt; c < ncb; c += G::kSize) {
         const int s = cs[c], e = cs[c + 1];
         i64 cid = 0;
-        if (e > s) cid = a.cell_id[sd[s]];  // issued now, consumed after the chain
+        if (e > s) cid = a.cell_id[sd[phys(s)]];  // issued now, consumed after the chain
         for (int i = e - 1; i > s; --i) {
-            const int j = s + jl[i];
-            const u32 x = sd[i], y = sd[j];
-            sd[i] = y;
-            sd[j] = x;
+            const int pi = phys(i);
+            const int pj = phys(s + jl[pi]);
+            const u32 x = sd[pi], y = sd[pj];
+            sd[pi] = y;
+            sd[pj] = x;
         }
         cidv[c] = cid;
     }
-    __syncthreads();
+    group_sync<kWarp>();
 
-    // ---- phase 4: one thread per pair slot (local window = positions lp0, lp0 + 1) --------
+    // ---- phase 4: two pair slots per thread and iteration ---------------------------------
     const double *mass = a.attributes + a.mass_row * a.n_sd;
     const bool flag_al = (((uintptr_t)a.is_first_in_pair) & 1) == 0;
-    const int n_iter = (P + 2 * kFusedThreads - 1) / (2 * kFusedThreads);
-    for (int it = 0; it < n_iter; ++it) {  // uniform trip count: warp-collective counter adds
-        const int lp0 = 2 * (it * kFusedThreads + tid), lp1 = lp0 + 1;
-        const i64 p0 = base_al + lp0;
-        const bool v0 = lp0 >= lo && lp0 < P, v1 = lp1 < P;
-        int cA = 0, cB = 0;
-        bool first0 = false, first1 = false, single0 = false, single1 = false;
-        if (v0) {
-            cA = cellof[lp0];
-            const bool even = ((lp0 - cs[cA]) & 1) == 0, partner = lp0 + 1 < cs[cA + 1];
-            first0 = even && partner;
-            single0 = even && !partner;
+    const bool vec_out = (((uintptr_t)a.idx_out) & 15) == 0;
+    for (int it = 0; it < n_iter; ++it) {  // uniform trip count: warp-collective code inside
+        // uniforms of this warp's 2 x 32 slots: 32 Philox blocks, one per lane (block b holds
+        // elements 2b, 2b + 1); lane x gets slot (h, x) from lane 16h + x/2
+        double rnd[2] = {0.0, 0.0};
+        if (kPhilox) {
+            const int lane = tid & 31, wig = (gt >> 5) << 5;  // first thread of my warp in group
+            const i64 d_it = (base_al + 4 * (i64)G::kSize * it) >> 1;  // even
+            const i64 d_mine = d_it + (i64)G::kSize * (lane >> 4) + wig + 2 * (lane & 15);
+            u32 w[4];
+            const u64 b = (u64)d_mine >> 1;
+            philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_rand, (u32)(a.call_rand >> 32),
+                          (u32)a.seed, (u32)(a.seed >> 32), w);
+            const double r0 = u01_from_words(w[0], w[1]), r1 = u01_from_words(w[2], w[3]);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int src = 16 * h + (lane >> 1);
+                const double e0 = __shfl_sync(0xffffffffu, r0, src);
+                const double e1 = __shfl_sync(0xffffffffu, r1, src);
+                rnd[h] = (lane & 1) ? e1 : e0;
+            }
         }
-        if (v1) {
-            cB = cellof[lp1];
-            const bool even = ((lp1 - cs[cB]) & 1) == 0, partner = lp1 + 1 < cs[cB + 1];
-            first1 = even && partner;
-            single1 = even && !partner;
-        }
-        // find_pairs output (pair_methods.py:38-41, :55)
-        if (v0 && v1 && flag_al) {
-            *reinterpret_cast<u16 *>(a.is_first_in_pair + p0) =
-                (u16)((first0 ? 1u : 0u) | (first1 ? 0x100u : 0u));
-        } else {
-            if (v0) a.is_first_in_pair[p0] = (u8)first0;
-            if (v1) a.is_first_in_pair[p0 + 1] = (u8)first1;
-        }
-        if (single0) a.idx_out[p0] = (i64)sd[lp0];
-        if (single1) a.idx_out[p0 + 1] = (i64)sd[lp1];
 
-        const bool has = first0 || first1;
-        const i64 d = p0 >> 1;  // global pair slot of this window
-        bool active = false;
-        i64 cid = 0, add_rate = 0, add_deficit = 0, add_coal = 0;
-        if (has) {
-            const int pf = first0 ? lp0 : lp1;
-            const int c = first0 ? cA : cB;
-            i64 j = (i64)sd[pf], k = (i64)sd[pf + 1];
-            i64 nj = a.multiplicity[j], nk = a.multiplicity[k];
-            double mj = 0.0, mk = 0.0;
-            if (K != KERNEL_CONSTANT_K) {
-                mj = mass[j];
-                mk = mass[k];
+        // stage A: find_pairs (pair_methods.py:38-41, :55) for my positions, pair members
+        bool has[2], dflt[2];
+        int pf[2], pcell[2];
+        i64 dslot[2], j[2], k[2], nj[2], nk[2];
+        double mj[2], mk[2], nf[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int lp0 = 4 * G::kSize * it + 2 * G::kSize * h + 2 * gt, lp1 = lp0 + 1;
+            const i64 p0 = base_al + lp0;
+            const bool v0 = lp0 >= lo && lp0 < P, v1 = lp1 >= lo && lp1 < P;
+            bool first0 = false, first1 = false, single0 = false, single1 = false;
+            int c0l = 0, c1l = 0;
+            if (v0) {
+                c0l = cellof[lp0];
+                const bool even = ((lp0 - cs[c0l]) & 1) == 0, partner = lp0 + 1 < cs[c0l + 1];
+                first0 = even && partner;
+                single0 = even && !partner;
             }
-            const double r = kPhilox ? philox_element(a.seed, a.call_rand, d) : a.rand[d];
-            const double nf =
-                norm_factor_of_rank(a.cell_start, a.cell_idx[a.cell_id[d]], a.timestep, a.dv);
-            if (nj < nk) {  // sort_within_pair_by_attr (ties keep order)
-                i64 t = j; j = k; k = t;
-                t = nj; nj = nk; nk = t;
-                double tm = mj; mj = mk; mk = tm;
+            if (v1) {
+                c1l = cellof[lp1];
+                const bool even = ((lp1 - cs[c1l]) & 1) == 0, partner = lp1 + 1 < cs[c1l + 1];
+                first1 = even && partner;
+                single1 = even && !partner;
             }
-            const i64 pg = base_al + pf;
-            a.idx_out[pg] = j;
-            a.idx_out[pg + 1] = k;
-            // volume = mass / rho_w (physics_methods.py:107-119); sum_pair; kernel; max_pair
-            double vsum = 0.0;
-            if (K != KERNEL_CONSTANT_K) vsum = mj / a.rho_w + mk / a.rho_w;
-            double prob = (double)nj * kernel_temp_of<K>(vsum, a.kernel_a, a.kernel_b);
-            prob = prob * nf;
-            prob = prob / a.substeps;
-            const double g_raw = ceil(prob - r);
-            if (g_raw == 0.0) {
-                a.gamma[d] = g_raw;  // keeps the sign of zero the reference stores
+            if (v0 && v1 && flag_al) {
+                *reinterpret_cast<u16 *>(a.is_first_in_pair + p0) =
+                    (u16)((first0 ? 1u : 0u) | (first1 ? 0x100u : 0u));
             } else {
-                const GammaResult g = sdm_gamma(g_raw, nj, nk);
-                a.gamma[d] = g.gamma;
-                cid = cidv[c];
-                add_rate = g.rate_add;
-                add_deficit = g.deficit_add;
-                active = true;
-                if (g.gamma != 0.0) {
-                    // coalesce, collisions_methods.py:44-59 (float arithmetic stored to int64)
-                    add_coal = (i64)(g.gamma * (double)nk);
-                    const double new_n = (double)nj - g.gamma * (double)nk;
-                    i64 nj_new, nk_new = nk;
-                    if (new_n > 0) {
-                        nj_new = (i64)new_n;
-                        a.multiplicity[j] = nj_new;
-                        for (i64 r_ = 0; r_ < a.n_attr; ++r_) {
-                            double *row = a.attributes + r_ * a.n_sd;
-                            const double aj = (r_ == a.mass_row && K != KERNEL_CONSTANT_K) ? mj : row[j];
-                            const double ak = (r_ == a.mass_row && K != KERNEL_CONSTANT_K) ? mk : row[k];
-                            row[k] = fma(g.gamma, aj, ak);
-                        }
-                    } else {
-                        nj_new = floordiv(nk, 2);
-                        nk_new = nk - nj_new;
-                        a.multiplicity[j] = nj_new;
-                        a.multiplicity[k] = nk_new;
-                        for (i64 r_ = 0; r_ < a.n_attr; ++r_) {
-                            double *row = a.attributes + r_ * a.n_sd;
-                            const double aj = (r_ == a.mass_row && K != KERNEL_CONSTANT_K) ? mj : row[j];
-                            const double ak = (r_ == a.mass_row && K != KERNEL_CONSTANT_K) ? mk : row[k];
-                            const double v = fma(g.gamma, aj, ak);
-                            row[j] = v;
-                            row[k] = v;
-                        }
-                    }
-                    if (nj_new == 0 || nk_new == 0) a.healthy[0] = 0;
+                if (v0) a.is_first_in_pair[p0] = (u8)first0;
+                if (v1) a.is_first_in_pair[p0 + 1] = (u8)first1;
+            }
+            if (single0) a.idx_out[p0] = (i64)sd[phys(lp0)];
+            if (single1) a.idx_out[p0 + 1] = (i64)sd[phys(lp1)];
+
+            const i64 d = p0 >> 1;
+            dslot[h] = d;
+            has[h] = first0 || first1;
+            pf[h] = first0 ? lp0 : lp1;
+            pcell[h] = first0 ? c0l : c1l;
+            dflt[h] = false;
+            j[h] = k[h] = 0;
+            nj[h] = nk[h] = 1;
+            mj[h] = mk[h] = nf[h] = 0.0;
+            if (has[h]) {
+                if (first0) {
+                    const uint2 t = *reinterpret_cast<const uint2 *>(sd + phys(lp0));
+                    j[h] = (i64)t.x;
+                    k[h] = (i64)t.y;
+                } else {
+                    j[h] = (i64)sd[phys(lp1)];
+                    k[h] = (i64)sd[phys(lp1 + 1)];
+                }
+            } else if (v0 && d < n_pairs_active) {
+                // no pair starts inside this window; the slot still goes through compute_gamma
+                // unless a pair starting at its second position, in the NEXT batch, owns it
+                bool next_first = false;
+                if (!v1) {  // lp0 is this batch's last position and p0 + 1 < length
+                    i64 rr = c1;
+                    while (rr < a.n_cell && a.cell_start[rr + 1] == end) ++rr;
+                    next_first = rr < a.n_cell && a.cell_start[rr + 1] - end >= 2;
+                }
+                dflt[h] = !next_first;
+            }
+            if (has[h] || dflt[h]) {
+                nf[h] = a.norm_factor[a.cell_idx[a.cell_id[d]]];  // quirk A1: raw cell_id[d]
+                if (!kPhilox) rnd[h] = a.rand[d];
+            }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (has[h]) {
+                nj[h] = a.multiplicity[j[h]];
+                nk[h] = a.multiplicity[k[h]];
+                if (K != KERNEL_CONSTANT_K) {
+                    mj[h] = mass[j[h]];
+                    mk[h] = mass[k[h]];
                 }
             }
-        } else if (v0 && d < n_pairs_active) {
-            // no pair starts inside this window; the slot still goes through compute_gamma.
-            // A pair starting at p0 + 1 in the NEXT batch owns the slot instead.
-            bool next_first = false;
-            if (!v1) {  // p0 is this batch's last position and p0 + 1 < length
-                i64 rr = c1;
-                while (rr < a.n_cell && a.cell_start[rr + 1] == end) ++rr;
-                next_first = rr < a.n_cell && a.cell_start[rr + 1] - end >= 2;
+
+        // stage B: sort within pair, probability, gamma, coalescence
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const i64 d = dslot[h];
+            bool active = false;
+            i64 cid = 0, add_rate = 0, add_deficit = 0, add_coal = 0;
+            if (has[h]) {
+                i64 sj = j[h], sk = k[h], n_j = nj[h], n_k = nk[h];
+                double m_j = mj[h], m_k = mk[h];
+                if (n_j < n_k) {  // sort_within_pair_by_attr (ties keep order)
+                    sj = k[h]; sk = j[h];
+                    n_j = nk[h]; n_k = nj[h];
+                    m_j = mk[h]; m_k = mj[h];
+                }
+                const i64 pg = base_al + pf[h];
+                if (vec_out && (pg & 1) == 0) {
+                    *reinterpret_cast<longlong2 *>(a.idx_out + pg) = make_longlong2(sj, sk);
+                } else {
+                    a.idx_out[pg] = sj;
+                    a.idx_out[pg + 1] = sk;
+                }
+                // volume = mass / rho_w (physics_methods.py:107-119); sum_pair; kernel; max_pair
+                double vsum = 0.0;
+                if (K != KERNEL_CONSTANT_K)
+                    vsum = div_by(m_j, a.rho_w, rho_rcp, rho_ok) + div_by(m_k, a.rho_w, rho_rcp, rho_ok);
+                const double f_nj = i64_to_f64(n_j);
+                double prob = f_nj * kernel_temp_of<K>(vsum, a.kernel_a, a.kernel_b);
+                prob = prob * nf[h];
+                if (!unit_substeps) prob = prob / a.substeps;
+                const double g_raw = ceil_exact(prob - rnd[h]);
+                if (g_raw == 0.0) {
+                    a.gamma[d] = g_raw;  // keeps the sign of zero the reference stores
+                } else {
+                    // compute_gamma, collisions_methods.py:546-558: g = min(int(gamma), n_j // n_k);
+                    // n_j >= n_k > 0 after the sort, so int(gamma) <= 1 needs no division
+                    const i64 gi = f64_to_i64(g_raw);
+                    i64 g = gi;
+                    if (gi > 1 || n_k <= 0) {
+                        const i64 prop = floordiv(n_j, n_k);
+                        g = gi < prop ? gi : prop;
+                    }
+                    const double gamma = i64_to_f64(g);
+                    a.gamma[d] = gamma;
+                    cid = cidv[pcell[h]];
+                    add_rate = g * n_k;
+                    add_deficit = (gi - g) * n_k;
+                    active = true;
+                    if (gamma != 0.0) {
+                        // coalesce, collisions_methods.py:44-59 (float arithmetic stored to int64)
+                        const double f_nk = i64_to_f64(n_k);
+                        const double gnk = gamma * f_nk;
+                        add_coal = f64_to_i64(gnk);
+                        const double new_n = f_nj - gnk;
+                        i64 nj_new, nk_new = n_k;
+                        const bool keep = new_n > 0;
+                        if (keep) {
+                            nj_new = f64_to_i64(new_n);
+                            a.multiplicity[sj] = nj_new;
+                        } else {
+                            nj_new = n_k >> 1;  // n_k // 2 (floor, also for negatives)
+                            nk_new = n_k - nj_new;
+                            a.multiplicity[sj] = nj_new;
+                            a.multiplicity[sk] = nk_new;
+                        }
+                        for (i64 r_ = 0; r_ < a.n_attr; ++r_) {
+                            double *row = a.attributes + r_ * a.n_sd;
+                            const bool cached = r_ == a.mass_row && K != KERNEL_CONSTANT_K;
+                            const double aj = cached ? m_j : row[sj];
+                            const double ak = cached ? m_k : row[sk];
+                            const double v = fma(gamma, aj, ak);
+                            row[sk] = v;
+                            if (!keep) row[sj] = v;
+                        }
+                        if (nj_new == 0 || nk_new == 0) a.healthy[0] = 0;
+                    }
+                }
+            } else if (dflt[h]) {
+                double prob = prob_nopair * nf[h];
+                if (!unit_substeps) prob = prob / a.substeps;
+                a.gamma[d] = ceil_exact(prob - rnd[h]);
             }
-            if (!next_first) {
-                const double r = kPhilox ? philox_element(a.seed, a.call_rand, d) : a.rand[d];
-                const double nf =
-                    norm_factor_of_rank(a.cell_start, a.cell_idx[a.cell_id[d]], a.timestep, a.dv);
-                a.gamma[d] = ceil(prob_nopair * nf / a.substeps - r);
-            }
+            counter_add<kAggregate>(a.collision_rate, cid, add_rate, active);
+            counter_add<kAggregate>(a.collision_rate_deficit, cid, add_deficit, active);
+            counter_add<kAggregate>(a.coalescence_rate, cid, add_coal, active);
         }
-        cell_counter_add(a.collision_rate, cid, add_rate, active);
-        cell_counter_add(a.collision_rate_deficit, cid, add_deficit, active);
-        cell_counter_add(a.coalescence_rate, cid, add_coal, active);
     }
 }
 
 // ---- launcher -----------------------------------------------------------------------------
-PYSDM_EXPORT int64_t pysdm_b200_fused_max_cell_size(void) { return kPosMax; }
+PYSDM_EXPORT int64_t pysdm_b200_fused_max_cell_size(void) { return kCtaPos; }
 
-template <int K, bool kPhilox>
+template <int K, bool kPhilox, bool kWarp, bool kAggregate>
 static int launch_fused(const FusedArgs &a, i64 n_batches, cudaStream_t st)
 {
     static bool configured = false;  // one caller thread per process (SURVEY 8b "Threading")
+    const int smem = Geo<kWarp>::kSmem;
     if (!configured) {
-        int err = (int)cudaFuncSetAttribute(k_fused_step<K, kPhilox>,
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            kFusedSmem);
+        int err = (int)cudaFuncSetAttribute(k_fused_step<K, kPhilox, kWarp, kAggregate>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (err) return err;
         configured = true;
     }
-    k_fused_step<K, kPhilox><<<(unsigned)n_batches, kFusedThreads, kFusedSmem, st>>>(a);
+    const i64 grid = (n_batches + Geo<kWarp>::kGroups - 1) / Geo<kWarp>::kGroups;
+    k_fused_step<K, kPhilox, kWarp, kAggregate>
+        <<<(unsigned)(grid < 1 ? 1 : grid), kFusedThreads, smem, st>>>(a);
     return LAUNCH_CHECK();
+}
+
+template <int K>
+static int dispatch_fused(const FusedArgs &a, i64 n_batches, bool philox, bool warp, bool aggregate,
+                          cudaStream_t st)
+{
+#define PYSDM_FUSED_CASE(P, W, A)                                                     \
+    if (philox == P && warp == W && aggregate == A) return launch_fused<K, P, W, A>(a, n_batches, st);
+    PYSDM_FUSED_CASE(false, false, false)
+    PYSDM_FUSED_CASE(false, false, true)
+    PYSDM_FUSED_CASE(false, true, false)
+    PYSDM_FUSED_CASE(false, true, true)
+    PYSDM_FUSED_CASE(true, false, false)
+    PYSDM_FUSED_CASE(true, false, true)
+    PYSDM_FUSED_CASE(true, true, false)
+    PYSDM_FUSED_CASE(true, true, true)
+#undef PYSDM_FUSED_CASE
+    return (int)cudaErrorInvalidValue;
+}
+
+// precondition of div_by(): b normal, moderate, significand not all ones
+static bool divisor_ok(double b)
+{
+    u64 bits;
+    memcpy(&bits, &b, sizeof bits);
+    const u64 mant = bits & 0x000FFFFFFFFFFFFFull;
+    const double m = b < 0 ? -b : b;
+    return m > 1e-10 && m < 1e10 && mant != 0x000FFFFFFFFFFFFFull;
 }
 
 PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *host_args,
@@ -337,25 +559,26 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
 {
     FusedArgs a = *host_args;
     if (a.n_sd <= 0 || a.n_sd >= ((i64)1 << 32) || a.n_cell <= 0) return (int)cudaErrorInvalidValue;
-    if (a.max_cell_size > kPosMax) return (int)cudaErrorInvalidConfiguration;
+    if (a.max_cell_size > kCtaPos) return (int)cudaErrorInvalidConfiguration;
     if ((a.u01 == nullptr) != (a.rand == nullptr)) return (int)cudaErrorInvalidValue;
-    i64 mcs = a.max_cell_size < 1 ? 1 : a.max_cell_size;
-    i64 cpb = kPosMax / mcs;
-    if (cpb > kCellMax) cpb = kCellMax;
-    a.cells_per_batch = cpb;
-    i64 n_batches = (a.n_cell + cpb - 1) / cpb;
     cudaStream_t st = (cudaStream_t)stream;
+    k_fused_norm_factor<<<grid_for(a.n_cell), kThreads, 0, st>>>(a.cell_start, a.n_cell,
+                                                                 a.norm_factor, a.timestep, a.dv);
+    const i64 mcs = a.max_cell_size < 1 ? 1 : a.max_cell_size;
+    const bool warp = mcs <= kWarpPos;
+    i64 cpb = (warp ? kWarpPos : kCtaPos) / mcs;
+    const i64 cap = warp ? kWarpCells : kCtaCells;
+    if (cpb > cap) cpb = cap;
+    a.cells_per_batch = cpb;
+    a.reserved = divisor_ok(a.rho_w) ? 1 : 0;
+    const i64 n_batches = (a.n_cell + cpb - 1) / cpb;
     const bool philox = a.u01 == nullptr;
+    const bool aggregate = a.n_cell < 64;  // few counters: aggregate within the warp first
     switch (a.kernel) {
-    case KERNEL_GOLOVIN:
-        return philox ? launch_fused<KERNEL_GOLOVIN, true>(a, n_batches, st)
-                      : launch_fused<KERNEL_GOLOVIN, false>(a, n_batches, st);
+    case KERNEL_GOLOVIN: return dispatch_fused<KERNEL_GOLOVIN>(a, n_batches, philox, warp, aggregate, st);
     case KERNEL_CONSTANT_K:
-        return philox ? launch_fused<KERNEL_CONSTANT_K, true>(a, n_batches, st)
-                      : launch_fused<KERNEL_CONSTANT_K, false>(a, n_batches, st);
-    case KERNEL_LINEAR:
-        return philox ? launch_fused<KERNEL_LINEAR, true>(a, n_batches, st)
-                      : launch_fused<KERNEL_LINEAR, false>(a, n_batches, st);
+        return dispatch_fused<KERNEL_CONSTANT_K>(a, n_batches, philox, warp, aggregate, st);
+    case KERNEL_LINEAR: return dispatch_fused<KERNEL_LINEAR>(a, n_batches, philox, warp, aggregate, st);
     default: return (int)cudaErrorInvalidValue;
     }
 }

@@ -6,7 +6,7 @@
 // ---- Philox4x32-10 -----------------------------------------------------------------
 // Element e of call number `call` under `seed` is a pure function of (seed, call, e):
 // counter = (e/2 lo, e/2 hi, call lo, call hi), key = (seed lo, seed hi); one Philox
-// block yields two doubles (53 random bits each, u = (x >> 11) * 2^-53 in [0, 1)).
+// block yields two doubles (52 random bits each, see u01_from_words).
 // Independent of launch geometry, so any kernel can regenerate element e in place.
 __device__ __forceinline__ void philox4x32_10(u32 c0, u32 c1, u32 c2, u32 c3, u32 k0, u32 k1,
                                               u32 out[4])
@@ -30,9 +30,10 @@ __device__ __forceinline__ void philox4x32_10(u32 c0, u32 c1, u32 c2, u32 c3, u3
     out[3] = c3;
 }
 
+// uniform in [0, 1) from 64 random bits: the top 52 bits fill the mantissa of a double in
+// [1, 2), minus 1 (resolution 2^-52; no integer->fp conversion instruction needed)
 __device__ __forceinline__ double u01_from_words(u32 hi, u32 lo)
 {
     u64 x = ((u64)hi << 32) | (u64)lo;
-    return (double)(x >> 11) * 0x1.0p-53;
+    return __longlong_as_double((long long)(0x3FF0000000000000ull | (x >> 12))) - 1.0;
 }
-

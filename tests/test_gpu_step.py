@@ -73,9 +73,10 @@ def test_reference_scenarios(name, fused):
 def ragged_population(seed, n_cell, mean, n_attr=1, max_mult=4):
     rng = np.random.default_rng(seed)
     sizes = rng.poisson(mean, n_cell)
-    sizes[rng.integers(0, n_cell, max(1, n_cell // 10))] = 0   # empty cells
-    sizes[rng.integers(0, n_cell, max(1, n_cell // 10))] = 1   # lonely SDs
-    sizes[rng.integers(0, n_cell, max(1, n_cell // 10))] = 3   # odd cells
+    if n_cell >= 5:
+        sizes[rng.integers(0, n_cell, max(1, n_cell // 10))] = 0   # empty cells
+        sizes[rng.integers(0, n_cell, max(1, n_cell // 10))] = 1   # lonely SDs
+        sizes[rng.integers(0, n_cell, max(1, n_cell // 10))] = 3   # odd cells
     cell_id = np.repeat(np.arange(n_cell), sizes)
     n_sd = len(cell_id)
     perm = rng.permutation(n_sd)  # SDs are NOT stored cell-contiguously
@@ -92,7 +93,7 @@ CASES = {
     "ragged_128": dict(seed=2, n_cell=300, mean=128, n_attr=3, dv=4e-7, steps=5),
     "big_cells": dict(seed=3, n_cell=5, mean=3000, n_attr=1, dv=2e-5, steps=3),
     "substeps": dict(seed=4, n_cell=64, mean=40, n_attr=2, dv=1e-7, steps=4, substeps=3),
-    "one_cell": dict(seed=5, n_cell=1, mean=5000, n_attr=1, dv=1e-4, steps=3),
+    "one_cell": dict(seed=5, n_cell=1, mean=5000, n_attr=1, dv=2e-6, steps=3),
 }
 
 

@@ -221,6 +221,9 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
 
     // ---- phase 2: stream idx + uniforms in, stage SD numbers and swap targets -------------
     {
+        const i64 *idx_b = a.idx_in + base_al;  // batch-local bases: 32-bit offsets below
+        const double *u01_b = kPhilox ? nullptr : a.u01 + base_al;
+        const u64 blk_b = (u64)base_al >> 1;    // Philox block of local position 0
         const bool vec_idx = (((uintptr_t)a.idx_in) & 15) == 0;
         const bool vec_u = !kPhilox && (((uintptr_t)a.u01) & 15) == 0;
         for (int it = 0; it < n_iter; ++it) {
@@ -229,34 +232,33 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int lp0 = 4 * G::kSize * it + 2 * G::kSize * h + 2 * gt;
-                const i64 p0 = base_al + lp0;
                 const bool v0 = lp0 >= lo && lp0 < P, v1 = lp0 + 1 < P;
                 sv[h][0] = sv[h][1] = 0;
                 uv[h][0] = uv[h][1] = 0.0;
                 if (v0 && v1 && vec_idx) {
-                    const longlong2 t = *reinterpret_cast<const longlong2 *>(a.idx_in + p0);
+                    const longlong2 t = *reinterpret_cast<const longlong2 *>(idx_b + (u32)lp0);
                     sv[h][0] = t.x;
                     sv[h][1] = t.y;
                 } else {
-                    if (v0) sv[h][0] = a.idx_in[p0];
-                    if (v1) sv[h][1] = a.idx_in[p0 + 1];
+                    if (v0) sv[h][0] = idx_b[(u32)lp0];
+                    if (v1) sv[h][1] = idx_b[(u32)lp0 + 1];
                 }
                 if (kPhilox) {
                     if (lp0 < P) {
                         u32 w[4];
-                        const u64 b = (u64)p0 >> 1;  // Philox block = elements 2b, 2b + 1
+                        const u64 b = blk_b + (u32)(lp0 >> 1);  // block = elements 2b, 2b + 1
                         philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_u01,
                                       (u32)(a.call_u01 >> 32), (u32)a.seed, (u32)(a.seed >> 32), w);
                         uv[h][0] = u01_from_words(w[0], w[1]);
                         uv[h][1] = u01_from_words(w[2], w[3]);
                     }
                 } else if (v0 && v1 && vec_u) {
-                    const double2 t = *reinterpret_cast<const double2 *>(a.u01 + p0);
+                    const double2 t = *reinterpret_cast<const double2 *>(u01_b + (u32)lp0);
                     uv[h][0] = t.x;
                     uv[h][1] = t.y;
                 } else {
-                    if (v0) uv[h][0] = a.u01[p0];
-                    if (v1) uv[h][1] = a.u01[p0 + 1];
+                    if (v0) uv[h][0] = u01_b[(u32)lp0];
+                    if (v1) uv[h][1] = u01_b[(u32)lp0 + 1];
                 }
             }
 #pragma unroll
@@ -273,10 +275,10 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
                     // 0 <= x < 2^33: floor by a round-down add, integer in the low mantissa bits
                     const double x = fd[2 * c] + uv[h][q] * fd[2 * c + 1];
                     const double t = __dadd_rd(x, kTwo52);
-                    i64 jr = (i64)((u64)__double_as_longlong(t) & 0x000FFFFFFFFFFFFFull) -
-                             (base_al + s);
+                    // j < 2^33: low word minus the low word of the cell's global start is exact
+                    int jr = (int)((u32)__double2loint(t) - (u32)(base_al + s));
                     if (jr >= len) jr = len - 1;  // fp round-up at huge cell_start (see index.cu)
-                    jrel[q] = (u32)jr;
+                    jrel[q] = (u32)phys(s + jr);  // skewed smem index of the swap target
                 }
                 if (lp0 >= lo && lp0 + 1 < P) {
                     const int ph = phys(lp0);
@@ -302,12 +304,13 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
         const int s = cs[c], e = cs[c + 1];
         i64 cid = 0;
         if (e > s) cid = a.cell_id[sd[phys(s)]];  // issued now, consumed after the chain
+        int pi = phys(e - 1);
         for (int i = e - 1; i > s; --i) {
-            const int pi = phys(i);
-            const int pj = phys(s + jl[pi]);
+            const int pj = jl[pi];
             const u32 x = sd[pi], y = sd[pj];
             sd[pi] = y;
             sd[pj] = x;
+            pi -= (i & 63) ? 1 : 3;  // phys(i - 1): two pad slots at every multiple of 64
         }
         cidv[c] = cid;
     }
@@ -317,16 +320,24 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
     const double *mass = a.attributes + a.mass_row * a.n_sd;
     const bool flag_al = (((uintptr_t)a.is_first_in_pair) & 1) == 0;
     const bool vec_out = (((uintptr_t)a.idx_out) & 15) == 0;
+    // batch-local bases (32-bit offsets in the loop); dl = local pair slot = lp0 / 2
+    u8 *flag_b = a.is_first_in_pair + base_al;
+    i64 *out_b = a.idx_out + base_al;
+    double *gamma_b = a.gamma + (base_al >> 1);
+    const i64 *cid_b = a.cell_id + (base_al >> 1);
+    const double *rand_b = kPhilox ? nullptr : a.rand + (base_al >> 1);
+    const i64 dl_left = n_pairs_active - (base_al >> 1);  // slots below go through compute_gamma
+    const int dl_active = dl_left > (i64)G::kPos ? G::kPos : (dl_left < 0 ? 0 : (int)dl_left);
     for (int it = 0; it < n_iter; ++it) {  // uniform trip count: warp-collective code inside
         // uniforms of this warp's 2 x 32 slots: 32 Philox blocks, one per lane (block b holds
         // elements 2b, 2b + 1); lane x gets slot (h, x) from lane 16h + x/2
         double rnd[2] = {0.0, 0.0};
         if (kPhilox) {
             const int lane = tid & 31, wig = (gt >> 5) << 5;  // first thread of my warp in group
-            const i64 d_it = (base_al + 4 * (i64)G::kSize * it) >> 1;  // even
-            const i64 d_mine = d_it + (i64)G::kSize * (lane >> 4) + wig + 2 * (lane & 15);
+            // local slot (even) whose block this lane computes; global slot = base_al/2 + it
+            const int dl_mine = 2 * G::kSize * it + G::kSize * (lane >> 4) + wig + 2 * (lane & 15);
             u32 w[4];
-            const u64 b = (u64)d_mine >> 1;
+            const u64 b = ((u64)base_al >> 2) + (u32)(dl_mine >> 1);
             philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_rand, (u32)(a.call_rand >> 32),
                           (u32)a.seed, (u32)(a.seed >> 32), w);
             const double r0 = u01_from_words(w[0], w[1]), r1 = u01_from_words(w[2], w[3]);
@@ -342,12 +353,12 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
         // stage A: find_pairs (pair_methods.py:38-41, :55) for my positions, pair members
         bool has[2], dflt[2];
         int pf[2], pcell[2];
-        i64 dslot[2], j[2], k[2], nj[2], nk[2];
+        u32 j[2], k[2];
+        i64 nj[2], nk[2];
         double mj[2], mk[2], nf[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int lp0 = 4 * G::kSize * it + 2 * G::kSize * h + 2 * gt, lp1 = lp0 + 1;
-            const i64 p0 = base_al + lp0;
             const bool v0 = lp0 >= lo && lp0 < P, v1 = lp1 >= lo && lp1 < P;
             bool first0 = false, first1 = false, single0 = false, single1 = false;
             int c0l = 0, c1l = 0;
@@ -364,17 +375,16 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
                 single1 = even && !partner;
             }
             if (v0 && v1 && flag_al) {
-                *reinterpret_cast<u16 *>(a.is_first_in_pair + p0) =
+                *reinterpret_cast<u16 *>(flag_b + (u32)lp0) =
                     (u16)((first0 ? 1u : 0u) | (first1 ? 0x100u : 0u));
             } else {
-                if (v0) a.is_first_in_pair[p0] = (u8)first0;
-                if (v1) a.is_first_in_pair[p0 + 1] = (u8)first1;
+                if (v0) flag_b[(u32)lp0] = (u8)first0;
+                if (v1) flag_b[(u32)lp1] = (u8)first1;
             }
-            if (single0) a.idx_out[p0] = (i64)sd[phys(lp0)];
-            if (single1) a.idx_out[p0 + 1] = (i64)sd[phys(lp1)];
+            if (single0) out_b[(u32)lp0] = (i64)sd[phys(lp0)];
+            if (single1) out_b[(u32)lp1] = (i64)sd[phys(lp1)];
 
-            const i64 d = p0 >> 1;
-            dslot[h] = d;
+            const u32 dl = (u32)lp0 >> 1;
             has[h] = first0 || first1;
             pf[h] = first0 ? lp0 : lp1;
             pcell[h] = first0 ? c0l : c1l;
@@ -385,13 +395,13 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
             if (has[h]) {
                 if (first0) {
                     const uint2 t = *reinterpret_cast<const uint2 *>(sd + phys(lp0));
-                    j[h] = (i64)t.x;
-                    k[h] = (i64)t.y;
+                    j[h] = t.x;
+                    k[h] = t.y;
                 } else {
-                    j[h] = (i64)sd[phys(lp1)];
-                    k[h] = (i64)sd[phys(lp1 + 1)];
+                    j[h] = sd[phys(lp1)];
+                    k[h] = sd[phys(lp1 + 1)];
                 }
-            } else if (v0 && d < n_pairs_active) {
+            } else if (v0 && (int)dl < dl_active) {
                 // no pair starts inside this window; the slot still goes through compute_gamma
                 // unless a pair starting at its second position, in the NEXT batch, owns it
                 bool next_first = false;
@@ -403,8 +413,8 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
                 dflt[h] = !next_first;
             }
             if (has[h] || dflt[h]) {
-                nf[h] = a.norm_factor[a.cell_idx[a.cell_id[d]]];  // quirk A1: raw cell_id[d]
-                if (!kPhilox) rnd[h] = a.rand[d];
+                nf[h] = a.norm_factor[a.cell_idx[cid_b[dl]]];  // quirk A1: raw cell_id[slot]
+                if (!kPhilox) rnd[h] = rand_b[dl];
             }
         }
 #pragma unroll
@@ -421,23 +431,24 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
         // stage B: sort within pair, probability, gamma, coalescence
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            const i64 d = dslot[h];
+            const u32 dl = (u32)(4 * G::kSize * it + 2 * G::kSize * h + 2 * gt) >> 1;
             bool active = false;
             i64 cid = 0, add_rate = 0, add_deficit = 0, add_coal = 0;
             if (has[h]) {
-                i64 sj = j[h], sk = k[h], n_j = nj[h], n_k = nk[h];
+                u32 sj = j[h], sk = k[h];
+                i64 n_j = nj[h], n_k = nk[h];
                 double m_j = mj[h], m_k = mk[h];
                 if (n_j < n_k) {  // sort_within_pair_by_attr (ties keep order)
                     sj = k[h]; sk = j[h];
                     n_j = nk[h]; n_k = nj[h];
                     m_j = mk[h]; m_k = mj[h];
                 }
-                const i64 pg = base_al + pf[h];
-                if (vec_out && (pg & 1) == 0) {
-                    *reinterpret_cast<longlong2 *>(a.idx_out + pg) = make_longlong2(sj, sk);
+                if (vec_out && (pf[h] & 1) == 0) {  // base_al is even: alignment of pf = of base_al + pf
+                    *reinterpret_cast<longlong2 *>(out_b + (u32)pf[h]) =
+                        make_longlong2((i64)sj, (i64)sk);
                 } else {
-                    a.idx_out[pg] = sj;
-                    a.idx_out[pg + 1] = sk;
+                    out_b[(u32)pf[h]] = (i64)sj;
+                    out_b[(u32)pf[h] + 1] = (i64)sk;
                 }
                 // volume = mass / rho_w (physics_methods.py:107-119); sum_pair; kernel; max_pair
                 double vsum = 0.0;
@@ -449,7 +460,7 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
                 if (!unit_substeps) prob = prob / a.substeps;
                 const double g_raw = ceil_exact(prob - rnd[h]);
                 if (g_raw == 0.0) {
-                    a.gamma[d] = g_raw;  // keeps the sign of zero the reference stores
+                    gamma_b[dl] = g_raw;  // keeps the sign of zero the reference stores
                 } else {
                     // compute_gamma, collisions_methods.py:546-558: g = min(int(gamma), n_j // n_k);
                     // n_j >= n_k > 0 after the sort, so int(gamma) <= 1 needs no division
@@ -460,7 +471,7 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
                         g = gi < prop ? gi : prop;
                     }
                     const double gamma = i64_to_f64(g);
-                    a.gamma[d] = gamma;
+                    gamma_b[dl] = gamma;
                     cid = cidv[pcell[h]];
                     add_rate = g * n_k;
                     add_deficit = (gi - g) * n_k;
@@ -497,7 +508,7 @@ __global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs
             } else if (dflt[h]) {
                 double prob = prob_nopair * nf[h];
                 if (!unit_substeps) prob = prob / a.substeps;
-                a.gamma[d] = ceil_exact(prob - rnd[h]);
+                gamma_b[dl] = ceil_exact(prob - rnd[h]);
             }
             counter_add<kAggregate>(a.collision_rate, cid, add_rate, active);
             counter_add<kAggregate>(a.collision_rate_deficit, cid, add_deficit, active);

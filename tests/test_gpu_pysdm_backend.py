@@ -1,0 +1,132 @@
+"""GPU drop-in test: the UNMODIFIED reference orchestration (Builder / Particulator /
+Coalescence / ParticleAttributes / Index / PairIndicator ... from PySDM itself) driven
+once by the reference's Numba backend and once by `pysdm_b200.B200`, same attributes, same
+uniform random numbers (HostReplayRandom = the Numba backend's PCG64 stream), compared
+after every step: permutation, pair flags, gamma, multiplicities, counters bit-exact,
+attributes bit-exact too for coalescence.
+
+Needs the reference importable: baseline/_ref (pip --target install of /root/reference,
+git-ignored, travels to the GPU box) or /root/reference; skipped otherwise.
+"""
+
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from .golden_util import assert_same_f64
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_REF = next((p for p in (os.path.join(ROOT, "baseline", "_ref"), "/root/reference")
+             if os.path.isdir(os.path.join(p, "PySDM"))), None)
+
+
+@pytest.fixture(scope="module")
+def pysdm():
+    if _REF is None:
+        pytest.skip("reference PySDM not available (baseline/_ref)")
+    os.environ.setdefault("NUMBA_NUM_THREADS", "1")
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "refshims"))
+    sys.path.insert(1, _REF)
+    np.NaN = np.nan  # the reference predates NumPy 2
+    import PySDM  # pylint: disable=import-outside-toplevel
+
+    return PySDM
+
+
+def build(pysdm, backend, *, n_sd, grid, dv, dt, attributes, dynamic_kw, kernel_b=1.5e3):
+    from PySDM import Builder  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics.collisions.collision_kernels import Golovin  # pylint: disable=import-outside-toplevel
+    from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
+    from PySDM.impl.mesh import Mesh  # pylint: disable=import-outside-toplevel
+
+    env = Box(dv=dv, dt=dt)
+    n_cell = int(np.prod(grid))
+    if n_cell > 1:
+        env.mesh = Mesh(grid, size=grid, dv=dv)
+    builder = Builder(n_sd=n_sd, backend=backend, environment=env)
+    builder.add_dynamic(Coalescence(collision_kernel=Golovin(b=kernel_b), **dynamic_kw))
+    attrs = {k: np.array(v) for k, v in attributes.items()}
+    if n_cell == 1:
+        attrs.pop("cell id", None)
+    return builder.build(attributes=attrs, products=())
+
+
+def snapshot(particulator):
+    dyn = particulator.dynamics["Collision"]
+    attrs = particulator.attributes
+    idx = attrs._ParticleAttributes__idx  # pylint: disable=protected-access
+
+    def host(storage):
+        return np.asarray(storage.to_ndarray())
+
+    return {
+        "length": int(idx.length),
+        "idx": host(idx),
+        "multiplicity": attrs["multiplicity"].to_ndarray(raw=True),
+        "attributes": attrs.get_extensive_attribute_storage().to_ndarray(raw=True),
+        "flag": host(dyn.is_first_in_pair.indicator),
+        "gamma": host(dyn.gamma),
+        "collision_rate": host(dyn.collision_rate),
+        "collision_rate_deficit": host(dyn.collision_rate_deficit),
+        "coalescence_rate": host(dyn.coalescence_rate),
+        "stats_n_substep": host(dyn.stats_n_substep),
+        "stats_dt_min": host(dyn.stats_dt_min),
+    }
+
+
+CASES = {
+    "local": dict(grid=(4, 5), n_sd=1500, dv=2e-8, kw=dict(adaptive=False, croupier="local")),
+    "global": dict(grid=(3, 3), n_sd=700, dv=2e-8, kw=dict(adaptive=False, croupier="global")),
+    "substeps": dict(grid=(3, 3), n_sd=700, dv=2e-8, kw=dict(adaptive=False, substeps=2)),
+    "adaptive": dict(grid=(3, 3), n_sd=700, dv=4e-9,
+                     kw=dict(adaptive=True, dt_coal_range=(0.01, 1.0))),
+    "adaptive_optrand": dict(grid=(3, 3), n_sd=700, dv=4e-9,
+                             kw=dict(adaptive=True, dt_coal_range=(0.05, 1.0),
+                                     optimized_random=True)),
+    "box": dict(grid=(1,), n_sd=1024, dv=1e-7, kw=dict(adaptive=False)),
+}
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_b200_backend_equals_numba_backend(pysdm, case):
+    from PySDM import Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200  # pylint: disable=import-outside-toplevel
+
+    c = CASES[case]
+    n_sd, n_cell = c["n_sd"], int(np.prod(c["grid"]))
+    rng = np.random.default_rng(99)
+    attributes = {
+        "multiplicity": rng.integers(1, 5, n_sd).astype(np.int64),
+        "volume": rng.exponential(4.0 / 3 * np.pi * (30.531e-6) ** 3, n_sd),
+        "cell id": rng.integers(0, n_cell, n_sd).astype(np.int64),
+    }
+    seed = 1234
+    common = dict(n_sd=n_sd, grid=c["grid"], dv=c["dv"], dt=1.0, attributes=attributes,
+                  dynamic_kw=c["kw"])
+    ref = build(pysdm, CPU(Formulae(fastmath=False, seed=seed)), **common)
+    sut = build(pysdm, B200(Formulae(fastmath=False, seed=seed), host_rng=True), **common)
+    collided = 0
+    for step in range(8):
+        ref.run(1)
+        sut.run(1)
+        a, b = snapshot(sut), snapshot(ref)
+        n = b["length"]
+        assert a["length"] == n, f"step {step}: length"
+        np.testing.assert_array_equal(a["idx"][:n], b["idx"][:n], f"step {step}: idx")
+        np.testing.assert_array_equal(a["flag"][:n], b["flag"][:n], f"step {step}: flag")
+        np.testing.assert_array_equal(a["multiplicity"], b["multiplicity"])
+        assert_same_f64(a["attributes"], b["attributes"], f"step {step}: attributes")
+        assert_same_f64(a["gamma"], b["gamma"], f"step {step}: gamma")
+        assert_same_f64(a["stats_dt_min"], b["stats_dt_min"], f"step {step}: stats_dt_min")
+        for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate",
+                  "stats_n_substep"):
+            np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
+        collided = int(b["coalescence_rate"].sum())
+    assert collided > 0

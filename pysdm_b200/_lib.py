@@ -8,7 +8,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libpysdm_b200.so")
+# PYSDM_B200_SO: tuning variants of the same sources (see pysdm_b200/build.py --out/-D)
+SO_PATH = os.environ.get("PYSDM_B200_SO") or os.path.join(_HERE, "libpysdm_b200.so")
 
 P = ctypes.c_void_p
 I64 = ctypes.c_int64

@@ -39,17 +39,21 @@ def is_stale():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_extension(force=False, verbose=False):
-    if not force and not is_stale():
+def build_extension(force=False, verbose=False, out=None, defines=()):
+    """`out`/`defines`: tuning variants (e.g. -DPYSDM_WARP_POS=768) built next to the default"""
+    if out is None and not force and not is_stale():
         return SO
-    cmd = [nvcc_path(), *NVCC_FLAGS, "-I", CSRC, "-I", INCLUDE, "-o", SO, *sources()]
+    out = out or SO
+    cmd = [nvcc_path(), *NVCC_FLAGS, *defines, "-I", CSRC, "-I", INCLUDE, "-o", out, *sources()]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))
     subprocess.check_call(cmd)
-    return SO
+    return out
 
 
 if __name__ == "__main__":
-    build_extension(force="--force" in sys.argv, verbose="-v" in sys.argv)
-    print(SO)
+    _out = sys.argv[sys.argv.index("--out") + 1] if "--out" in sys.argv else None
+    _defs = tuple(a for a in sys.argv[1:] if a.startswith("-D"))
+    print(build_extension(force="--force" in sys.argv, verbose="-v" in sys.argv, out=_out,
+                          defines=_defs))

@@ -41,9 +41,15 @@ typedef pysdm_b200_fused_args FusedArgs;
 
 enum { KERNEL_GOLOVIN = 0, KERNEL_CONSTANT_K = 1, KERNEL_LINEAR = 2 };
 
+#ifndef PYSDM_WARP_POS
+#define PYSDM_WARP_POS 1024
+#endif
+#ifndef PYSDM_MIN_CTAS
+#define PYSDM_MIN_CTAS 3
+#endif
 constexpr int kFusedThreads = 256;
 constexpr int kCtaPos = 8192, kCtaCells = 256;  // CTA group: positions / cells per batch
-constexpr int kWarpPos = 1024, kWarpCells = 32;  // warp group
+constexpr int kWarpPos = PYSDM_WARP_POS, kWarpCells = 32;  // warp group
 constexpr double kTwo52 = 4503599627370496.0;    // 2^52
 
 // ---- exact arithmetic helpers without XU-pipe instructions ---------------------------------
@@ -150,7 +156,7 @@ __device__ __forceinline__ void counter_add(i64 *counters, i64 cid, i64 value, b
 }
 
 template <int K, bool kPhilox, bool kWarp, bool kAggregate>
-__global__ void __launch_bounds__(kFusedThreads, 3) k_fused_step(const FusedArgs a)
+__global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(const FusedArgs a)
 {
     typedef Geo<kWarp> G;
     extern __shared__ __align__(16) unsigned char smem_all[];

@@ -29,6 +29,7 @@ def pysdm():
     if _REF is None:
         pytest.skip("reference PySDM not available (baseline/_ref)")
     os.environ.setdefault("NUMBA_NUM_THREADS", "1")
+    os.environ.setdefault("CI", "1")  # the reference's own switch: no ThrustRTC import (not installed)
     sys.path.insert(0, os.path.join(ROOT, "oracle", "refshims"))
     sys.path.insert(1, _REF)
     np.NaN = np.nan  # the reference predates NumPy 2

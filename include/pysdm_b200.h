@@ -194,6 +194,11 @@ typedef struct pysdm_b200_fused_args {
     int32_t kernel;             /* 0 Golovin, 1 ConstantK, 2 Linear */
     int32_t reserved;
     int64_t max_cell_size;      /* upper bound of cell_start[c+1]-cell_start[c] (host hint) */
+    double *nf_slot;            /* [n_sd / 2] scratch: norm_factor[cell_idx[cell_id[d]]] per pair
+                                   slot d (the factor `normalize` applies, :647-648) */
+    int64_t refresh_nf;         /* != 0: recompute norm_factor and nf_slot first.  Must be set
+                                   whenever cell_start, cell_idx, cell_id, timestep or dv changed
+                                   since the previous call with the same nf_slot buffer */
 } pysdm_b200_fused_args;
 
 int64_t pysdm_b200_fused_max_cell_size(void);

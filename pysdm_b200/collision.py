@@ -118,6 +118,8 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.collision_rate_deficit = full(self.n_cell, 0, i64)
         self.coalescence_rate = full(self.n_cell, 0, i64)
         self.status = full(1, 0, i64)
+        self.nf_slot = full(n_pairs, nan, f64)  # fused step: normalize factor per pair slot
+        self.nf_valid = False  # False after anything that changes cell_start/cell_idx/cell_id
         # RandomGeneratorOptimizer.register
         self.optimized_random = optimized_random
         shift = math.ceil(dt / dt_coal_range[0]) if optimized_random else 0
@@ -150,6 +152,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.sorted = True
         self.sorted_length = self.length  # = cell_start[-1], kept on the host
         self.max_cell = None
+        self.nf_valid = False
 
     def get_cell_start(self):
         if not self.sorted:
@@ -252,14 +255,16 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             coalescence_rate=self.coalescence_rate, healthy=self.healthy, status=self.status,
             length=self.length, max_cell=self.max_cell, kernel=self.kernel.fused,
             kernel_a=self.kernel.a, kernel_b=self.kernel.b, timestep=self.dt, dv=self.dv,
-            rho_w=self.rho_w, substeps=self.substeps, **kw)
+            rho_w=self.rho_w, substeps=self.substeps, nf_slot=self.nf_slot,
+            refresh_nf=not self.nf_valid, **kw)
         m.check(err, "fused_collision_step")
+        self.n_launches += 1 if self.nf_valid else 3
+        self.nf_valid = True
         # positions beyond the working length keep their content (flagged SDs)
         if self.length < self.n_sd:
             self.tmp_idx[self.length:] = self.idx[self.length:]
         self.idx, self.tmp_idx = self.tmp_idx, self.idx
         self.n_fused_steps += 1
-        self.n_launches += 2  # norm_factor pre-pass + the fused step
 
     def step_methods(self):
         """the reference's sequence of backend calls, one kernel (group) each"""

@@ -111,6 +111,17 @@ __global__ void k_fused_norm_factor(const i64 *__restrict__ cell_start, i64 n_ce
         norm_factor[r] = sdm_norm_factor(cell_start[r + 1] - cell_start[r], timestep, dv);
 }
 
+// per pair slot d: the factor normalize() multiplies prob[d] with (collisions_methods.py:647-648:
+// norm_factor[cell_idx[cell_id[d]]], d used as a PARTICLE number -- reference quirk A1).  It only
+// changes when cell_start / cell_idx / cell_id / dt / dv change, so it is cached across steps.
+__global__ void k_fused_nf_slot(const i64 *__restrict__ cell_id, const i64 *__restrict__ cell_idx,
+                                const double *__restrict__ norm_factor, double *__restrict__ nf_slot,
+                                i64 n_slots)
+{
+    i64 d = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d < n_slots) nf_slot[d] = norm_factor[cell_idx[cell_id[d]]];
+}
+
 // ---- group geometry -----------------------------------------------------------------------
 template <bool kWarp>
 struct Geo {
@@ -181,7 +192,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     // ---- tail: pair slots beyond the working length keep `0 * norm_factor` ------------
     for (i64 d = n_pairs_active + (i64)blockIdx.x * kFusedThreads + tid; d < a.n_sd / 2;
          d += (i64)gridDim.x * kFusedThreads)
-        a.gamma[d] = prob_nopair * a.norm_factor[a.cell_idx[a.cell_id[d]]] / a.substeps;
+        a.gamma[d] = prob_nopair * a.nf_slot[d] / a.substeps;
 
     const i64 batch = (i64)blockIdx.x * G::kGroups + group;
     const i64 c0 = batch * a.cells_per_batch;
@@ -232,6 +243,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
         const u64 blk_b = (u64)base_al >> 1;    // Philox block of local position 0
         const bool vec_idx = (((uintptr_t)a.idx_in) & 15) == 0;
         const bool vec_u = !kPhilox && (((uintptr_t)a.u01) & 15) == 0;
+#pragma unroll 2
         for (int it = 0; it < n_iter; ++it) {
             i64 sv[2][2];
             double uv[2][2];
@@ -330,7 +342,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     u8 *flag_b = a.is_first_in_pair + base_al;
     i64 *out_b = a.idx_out + base_al;
     double *gamma_b = a.gamma + (base_al >> 1);
-    const i64 *cid_b = a.cell_id + (base_al >> 1);
+    const double *nf_b = a.nf_slot + (base_al >> 1);
     const double *rand_b = kPhilox ? nullptr : a.rand + (base_al >> 1);
     const i64 dl_left = n_pairs_active - (base_al >> 1);  // slots below go through compute_gamma
     const int dl_active = dl_left > (i64)G::kPos ? G::kPos : (dl_left < 0 ? 0 : (int)dl_left);
@@ -419,7 +431,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
                 dflt[h] = !next_first;
             }
             if (has[h] || dflt[h]) {
-                nf[h] = a.norm_factor[a.cell_idx[cid_b[dl]]];  // quirk A1: raw cell_id[slot]
+                nf[h] = nf_b[dl];  // norm_factor[cell_idx[cell_id[slot]]] (quirk A1), cached
                 if (!kPhilox) rnd[h] = rand_b[dl];
             }
         }
@@ -579,8 +591,14 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
     if (a.max_cell_size > kCtaPos) return (int)cudaErrorInvalidConfiguration;
     if ((a.u01 == nullptr) != (a.rand == nullptr)) return (int)cudaErrorInvalidValue;
     cudaStream_t st = (cudaStream_t)stream;
-    k_fused_norm_factor<<<grid_for(a.n_cell), kThreads, 0, st>>>(a.cell_start, a.n_cell,
-                                                                 a.norm_factor, a.timestep, a.dv);
+    if (a.nf_slot == nullptr) return (int)cudaErrorInvalidValue;
+    if (a.refresh_nf) {
+        k_fused_norm_factor<<<grid_for(a.n_cell), kThreads, 0, st>>>(
+            a.cell_start, a.n_cell, a.norm_factor, a.timestep, a.dv);
+        if (a.n_sd / 2 > 0)
+            k_fused_nf_slot<<<grid_for(a.n_sd / 2), kThreads, 0, st>>>(
+                a.cell_id, a.cell_idx, a.norm_factor, a.nf_slot, a.n_sd / 2);
+    }
     const i64 mcs = a.max_cell_size < 1 ? 1 : a.max_cell_size;
     const bool warp = mcs <= kWarpPos;
     i64 cpb = (warp ? kWarpPos : kCtaPos) / mcs;

@@ -139,7 +139,8 @@ struct Geo {
     static constexpr int kCs = ((kCells + 1) * 4 + 15) / 16 * 16;  // i32 local cell starts
     static constexpr int kFd = kCells * 16;                        // double S, len per cell
     static constexpr int kCid = kCells * 8;                        // i64 cell id per cell
-    static constexpr int kBytes = kSd + kJl + kCo + kCs + kFd + kCid;
+    static constexpr int kQueue = (kSize / 32) * 64 * 12;          // per warp: 64 x (f64 + u32)
+    static constexpr int kBytes = kSd + kJl + kCo + kCs + kFd + kCid + kQueue;
     static constexpr int kSmem = kBytes * kGroups;
 };
 
@@ -166,6 +167,70 @@ __device__ __forceinline__ void counter_add(i64 *counters, i64 cid, i64 value, b
         atomicAdd((unsigned long long *)&counters[cid], (unsigned long long)value);
 }
 
+// ---- colliding pairs, one per lane: gamma cap, rate counters, coalescence ---------------------
+// (compute_gamma :546-558 and collision_coalescence/coalesce :44-59,:418-477 of
+// impl_numba/methods/collisions_methods.py).  Called with the whole warp converged; `mine`
+// tells whether this lane holds an entry: pf = local position of the pair's first member,
+// g_raw = ceil(prob - rand) != 0.  The pair is re-read from shared memory and re-sorted by
+// multiplicity (cheap, cached) instead of being carried through the queue.
+template <int K, bool kAggregate>
+__device__ __forceinline__ void process_hits(const FusedArgs &a, u32 pf, double g_raw, bool mine,
+                                             const u32 *sd, const u8 *cellof, const i64 *cidv,
+                                             double *gamma_b)
+{
+    bool active = false;
+    i64 cid = 0, add_rate = 0, add_deficit = 0, add_coal = 0;
+    if (mine) {
+        u32 sj = sd[phys((int)pf)], sk = sd[phys((int)pf + 1)];
+        i64 n_j = a.multiplicity[sj], n_k = a.multiplicity[sk];
+        if (n_j < n_k) {  // sort_within_pair_by_attr (ties keep order)
+            const u32 t = sj; sj = sk; sk = t;
+            const i64 tn = n_j; n_j = n_k; n_k = tn;
+        }
+        // g = min(int(gamma), n_j // n_k); n_j >= n_k > 0 here, so int(gamma) <= 1 needs no division
+        const i64 gi = f64_to_i64(g_raw);
+        i64 g = gi;
+        if (gi > 1 || n_k <= 0) {
+            const i64 prop = floordiv(n_j, n_k);
+            g = gi < prop ? gi : prop;
+        }
+        const double gamma = i64_to_f64(g);
+        if (g != gi) gamma_b[pf >> 1] = gamma;
+        cid = cidv[cellof[pf]];
+        add_rate = g * n_k;
+        add_deficit = (gi - g) * n_k;
+        active = true;
+        if (gamma != 0.0) {
+            // coalesce: float arithmetic stored to int64 (quirk A7), attribute update fused (fma)
+            const double f_nj = i64_to_f64(n_j), f_nk = i64_to_f64(n_k);
+            const double gnk = gamma * f_nk;
+            add_coal = f64_to_i64(gnk);
+            const double new_n = f_nj - gnk;
+            i64 nj_new, nk_new = n_k;
+            const bool keep = new_n > 0;
+            if (keep) {
+                nj_new = f64_to_i64(new_n);
+                a.multiplicity[sj] = nj_new;
+            } else {
+                nj_new = n_k >> 1;  // n_k // 2 (floor, also for negatives)
+                nk_new = n_k - nj_new;
+                a.multiplicity[sj] = nj_new;
+                a.multiplicity[sk] = nk_new;
+            }
+            for (i64 r_ = 0; r_ < a.n_attr; ++r_) {
+                double *row = a.attributes + r_ * a.n_sd;
+                const double v = fma(gamma, row[sj], row[sk]);
+                row[sk] = v;
+                if (!keep) row[sj] = v;
+            }
+            if (nj_new == 0 || nk_new == 0) a.healthy[0] = 0;
+        }
+    }
+    counter_add<kAggregate>(a.collision_rate, cid, add_rate, active);
+    counter_add<kAggregate>(a.collision_rate_deficit, cid, add_deficit, active);
+    counter_add<kAggregate>(a.coalescence_rate, cid, add_coal, active);
+}
+
 template <int K, bool kPhilox, bool kWarp, bool kAggregate>
 __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(const FusedArgs a)
 {
@@ -181,6 +246,12 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     i32 *cs = reinterpret_cast<i32 *>(smem + G::kSd + G::kJl + G::kCo);
     double *fd = reinterpret_cast<double *>(smem + G::kSd + G::kJl + G::kCo + G::kCs);
     i64 *cidv = reinterpret_cast<i64 *>(smem + G::kSd + G::kJl + G::kCo + G::kCs + G::kFd);
+    // per-warp queue of colliding pairs: g_raw (f64) and local position of the pair's first (u32)
+    unsigned char *qbase = smem + G::kSd + G::kJl + G::kCo + G::kCs + G::kFd + G::kCid +
+                           (kWarp ? 0 : (tid >> 5) * 64 * 12);
+    double *q_g = reinterpret_cast<double *>(qbase);
+    u32 *q_pf = reinterpret_cast<u32 *>(qbase + 64 * 8);
+    int qn = 0;  // warp-uniform fill level
 
     const i64 n_pairs_active = a.length / 2;
     // literal chain for a slot without a pair: max_pair -> 0; *= kernel_temp; normalize
@@ -446,19 +517,19 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
                 }
             }
 
-        // stage B: sort within pair, probability, gamma, coalescence
+        // stage B: sort within pair, probability, gamma.  Pairs that do collide (gamma != 0, a
+        // few per cent) are queued per warp and handled with full lanes by process_hits()
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const u32 dl = (u32)(4 * G::kSize * it + 2 * G::kSize * h + 2 * gt) >> 1;
-            bool active = false;
-            i64 cid = 0, add_rate = 0, add_deficit = 0, add_coal = 0;
+            double g_raw = 0.0;
             if (has[h]) {
                 u32 sj = j[h], sk = k[h];
-                i64 n_j = nj[h], n_k = nk[h];
+                i64 n_j = nj[h];
                 double m_j = mj[h], m_k = mk[h];
-                if (n_j < n_k) {  // sort_within_pair_by_attr (ties keep order)
+                if (nj[h] < nk[h]) {  // sort_within_pair_by_attr (ties keep order)
                     sj = k[h]; sk = j[h];
-                    n_j = nk[h]; n_k = nj[h];
+                    n_j = nk[h];
                     m_j = mk[h]; m_k = mj[h];
                 }
                 if (vec_out && (pf[h] & 1) == 0) {  // base_al is even: alignment of pf = of base_al + pf
@@ -472,66 +543,38 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
                 double vsum = 0.0;
                 if (K != KERNEL_CONSTANT_K)
                     vsum = div_by(m_j, a.rho_w, rho_rcp, rho_ok) + div_by(m_k, a.rho_w, rho_rcp, rho_ok);
-                const double f_nj = i64_to_f64(n_j);
-                double prob = f_nj * kernel_temp_of<K>(vsum, a.kernel_a, a.kernel_b);
+                double prob = i64_to_f64(n_j) * kernel_temp_of<K>(vsum, a.kernel_a, a.kernel_b);
                 prob = prob * nf[h];
                 if (!unit_substeps) prob = prob / a.substeps;
-                const double g_raw = ceil_exact(prob - rnd[h]);
-                if (g_raw == 0.0) {
-                    gamma_b[dl] = g_raw;  // keeps the sign of zero the reference stores
-                } else {
-                    // compute_gamma, collisions_methods.py:546-558: g = min(int(gamma), n_j // n_k);
-                    // n_j >= n_k > 0 after the sort, so int(gamma) <= 1 needs no division
-                    const i64 gi = f64_to_i64(g_raw);
-                    i64 g = gi;
-                    if (gi > 1 || n_k <= 0) {
-                        const i64 prop = floordiv(n_j, n_k);
-                        g = gi < prop ? gi : prop;
-                    }
-                    const double gamma = i64_to_f64(g);
-                    gamma_b[dl] = gamma;
-                    cid = cidv[pcell[h]];
-                    add_rate = g * n_k;
-                    add_deficit = (gi - g) * n_k;
-                    active = true;
-                    if (gamma != 0.0) {
-                        // coalesce, collisions_methods.py:44-59 (float arithmetic stored to int64)
-                        const double f_nk = i64_to_f64(n_k);
-                        const double gnk = gamma * f_nk;
-                        add_coal = f64_to_i64(gnk);
-                        const double new_n = f_nj - gnk;
-                        i64 nj_new, nk_new = n_k;
-                        const bool keep = new_n > 0;
-                        if (keep) {
-                            nj_new = f64_to_i64(new_n);
-                            a.multiplicity[sj] = nj_new;
-                        } else {
-                            nj_new = n_k >> 1;  // n_k // 2 (floor, also for negatives)
-                            nk_new = n_k - nj_new;
-                            a.multiplicity[sj] = nj_new;
-                            a.multiplicity[sk] = nk_new;
-                        }
-                        for (i64 r_ = 0; r_ < a.n_attr; ++r_) {
-                            double *row = a.attributes + r_ * a.n_sd;
-                            const bool cached = r_ == a.mass_row && K != KERNEL_CONSTANT_K;
-                            const double aj = cached ? m_j : row[sj];
-                            const double ak = cached ? m_k : row[sk];
-                            const double v = fma(gamma, aj, ak);
-                            row[sk] = v;
-                            if (!keep) row[sj] = v;
-                        }
-                        if (nj_new == 0 || nk_new == 0) a.healthy[0] = 0;
-                    }
-                }
+                g_raw = ceil_exact(prob - rnd[h]);
+                gamma_b[dl] = g_raw;  // final unless capped by n_j // n_k (process_hits)
             } else if (dflt[h]) {
                 double prob = prob_nopair * nf[h];
                 if (!unit_substeps) prob = prob / a.substeps;
                 gamma_b[dl] = ceil_exact(prob - rnd[h]);
             }
-            counter_add<kAggregate>(a.collision_rate, cid, add_rate, active);
-            counter_add<kAggregate>(a.collision_rate_deficit, cid, add_deficit, active);
-            counter_add<kAggregate>(a.coalescence_rate, cid, add_coal, active);
+            // queue the hits of this warp (g_raw == 0, also -0, means no collision)
+            const bool hit = has[h] && g_raw != 0.0;
+            const unsigned hits = __ballot_sync(0xffffffffu, hit);
+            if (hit) {
+                const int slot = qn + __popc(hits & ((1u << (tid & 31)) - 1u));
+                q_pf[slot] = (u32)pf[h];
+                q_g[slot] = g_raw;
+            }
+            qn += __popc(hits);
+            __syncwarp();
+            if (qn >= 32) {
+                qn -= 32;
+                process_hits<K, kAggregate>(a, q_pf[qn + (tid & 31)], q_g[qn + (tid & 31)], true, sd,
+                                            cellof, cidv, gamma_b);
+                __syncwarp();
+            }
         }
+    }
+    if (qn > 0) {
+        const bool mine = (tid & 31) < qn;
+        process_hits<K, kAggregate>(a, mine ? q_pf[tid & 31] : 0u, mine ? q_g[tid & 31] : 0.0, mine, sd,
+                                    cellof, cidv, gamma_b);
     }
 }
 

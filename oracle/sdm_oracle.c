@@ -446,7 +446,7 @@ static inline void compute_transfer_multiplicities(double gamma, i64 j, i64 k,
     double take_from_j_test = (double)multiplicity[k];
     double take_from_j = 0;
     double new_mult_k_test =
-        ((particle_mass[j] + particle_mass[k]) / fragment_mass_i) * (double)multiplicity[k];
+        ((particle_mass[j] + particle_mass[k]) * (double)multiplicity[k]) / fragment_mass_i;
     double new_mult_k = (double)multiplicity[k];
     i64 g = (i64)gamma;
     for (i64 m = 0; m < g; ++m) {
@@ -459,8 +459,7 @@ static inline void compute_transfer_multiplicities(double gamma, i64 j, i64 k,
         new_mult_k = new_mult_k_test;
         gamma_j_k = m + 1;
         take_from_j_test += new_mult_k_test;
-        new_mult_k_test =
-            new_mult_k_test * (particle_mass[j] / fragment_mass_i) + new_mult_k_test;
+        new_mult_k_test = fma(new_mult_k_test, particle_mass[j] / fragment_mass_i, new_mult_k_test);
     }
     *take_from_j_out = take_from_j;
     *new_mult_k_out = new_mult_k;
@@ -476,11 +475,10 @@ static inline void get_new_multiplicities_and_update_attributes(i64 j, i64 k, do
                                                                 double new_mult_k, double *nj,
                                                                 double *nk)
 {
+    const double recip = 1.0 / new_mult_k;
     for (i64 a = 0; a < n_attr; ++a) {
         double *ak = &attributes[a * n_sd + k];
-        *ak *= (double)multiplicity[k];
-        *ak += take_from_j * attributes[a * n_sd + j];
-        *ak /= new_mult_k;
+        *ak = fma(take_from_j, attributes[a * n_sd + j], (double)multiplicity[k] * *ak) * recip;
     }
     if ((double)multiplicity[j] > take_from_j) {
         *nj = (double)multiplicity[j] - take_from_j;
@@ -503,11 +501,11 @@ static inline void round_multiplicities_to_ints_and_update_attributes(i64 j, i64
     i64 rj = (i64)rint(nj), rk = (i64)rint(nk);
     multiplicity[j] = rj > 1 ? rj : 1;
     multiplicity[k] = rk > 1 ? rk : 1;
-    double factor_j = nj / (double)multiplicity[j];
-    double factor_k = nk / (double)multiplicity[k];
+    double rcp_j = 1.0 / (double)multiplicity[j];
+    double rcp_k = 1.0 / (double)multiplicity[k];
     for (i64 a = 0; a < n_attr; ++a) {
-        attributes[a * n_sd + k] *= factor_k;
-        attributes[a * n_sd + j] *= factor_j;
+        attributes[a * n_sd + k] = (attributes[a * n_sd + k] * nk) * rcp_k;
+        attributes[a * n_sd + j] = (attributes[a * n_sd + j] * nj) * rcp_j;
     }
 }
 

@@ -23,8 +23,8 @@ ptr = ctypes.c_void_p
 
 def build(force=False):
     """compile the C restatement with the system gcc (seconds)"""
-    src = os.path.join(_HERE, "sdm_oracle.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("sdm_oracle.c", "sdm_physics.c", "Makefile")]
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(map(os.path.getmtime, srcs)):
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
     return _SO
 
@@ -201,3 +201,95 @@ def collision_coalescence_breakup(multiplicity, idx, length, attributes, gamma, 
         _pi(coalescence_rate), _pi(breakup_rate), _pi(breakup_rate_deficit),
         _pb(is_first_in_pair), f64(max_multiplicity), _pf(particle_mass),
         ctypes.c_int(int(handle_all_breakups))))
+
+
+# ---- physics rows (oracle/sdm_physics.c) ---------------------------------------------
+def power(x, exponent):
+    """Storage.__ipow__: sign(x) * |x| ** exponent, in place"""
+    lib().oracle_power(_pf(x), i64(len(x)), f64(exponent))
+
+
+def product_scalar(out, in_, scalar):
+    lib().oracle_product_scalar(_pf(out), _pf(in_), f64(scalar), i64(len(out)))
+
+
+def interpolation(output, radius, factor, b, c):
+    lib().oracle_interpolation(_pf(output), _pf(radius), i64(len(radius)), f64(factor), _pf(b),
+                               _pf(c))
+
+
+def terminal_velocity_rogers_yau(values, radius, params):
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    lib().oracle_terminal_velocity_rogers_yau(_pf(values), _pf(radius), i64(len(values)),
+                                              _pf(params))
+
+
+def power_series(values, radius, prefactors, powers):
+    prefactors = np.ascontiguousarray(prefactors, dtype=np.float64)
+    powers = np.ascontiguousarray(powers, dtype=np.float64)
+    lib().oracle_power_series(_pf(values), _pf(radius), i64(len(values)), i64(len(powers)),
+                              _pf(prefactors), _pf(powers))
+
+
+def int_mask_of(params):
+    """bit e set when params[e] is a Python/numpy integer (see sdm_physics.c)"""
+    return sum(1 << e for e, v in enumerate(params) if isinstance(v, (int, np.integer)))
+
+
+def linear_collection_efficiency(params, int_mask, output, radii, is_first_in_pair, idx, length,
+                                 unit):
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    lib().oracle_linear_collection_efficiency(
+        _pf(params), i64(int_mask), _pf(output), i64(len(output)), _pf(radii),
+        _pb(is_first_in_pair), _pi(idx), i64(length), f64(unit))
+
+
+def fragmentation_limiters(n_fragment, frag_volume, vmin, nfmax, x_plus_y):
+    lib().oracle_fragmentation_limiters(
+        _pf(n_fragment), _pf(frag_volume), i64(len(frag_volume)), f64(vmin),
+        ctypes.c_int(nfmax is not None), f64(0.0 if nfmax is None else nfmax), _pf(x_plus_y))
+
+
+def slams_fragmentation(n_fragment, frag_volume, x_plus_y, probs, rand, vmin, nfmax):
+    lib().oracle_slams_fragmentation(_pf(n_fragment), _pf(frag_volume), _pf(x_plus_y), _pf(probs),
+                                     _pf(rand), i64(len(rand)))
+    fragmentation_limiters(n_fragment, frag_volume, vmin, nfmax, x_plus_y)
+
+
+def exp_fragmentation(n_fragment, scale, frag_volume, x_plus_y, rand, vmin, nfmax, tol=1e-5):
+    lib().oracle_exp_fragmentation(f64(scale), _pf(frag_volume), _pf(rand), i64(len(rand)),
+                                   f64(tol))
+    fragmentation_limiters(n_fragment, frag_volume, vmin, nfmax, x_plus_y)
+
+
+def feingold1988_fragmentation(n_fragment, scale, frag_volume, x_plus_y, rand, fragtol, vmin,
+                               nfmax):
+    lib().oracle_feingold1988_fragmentation(f64(scale), _pf(frag_volume), _pf(x_plus_y),
+                                            _pf(rand), i64(len(rand)), f64(fragtol))
+    fragmentation_limiters(n_fragment, frag_volume, vmin, nfmax, x_plus_y)
+
+
+def gauss_fragmentation(n_fragment, mu, sigma, frag_volume, x_plus_y, rand, vmin, nfmax):
+    lib().oracle_gauss_fragmentation(f64(mu), f64(sigma), _pf(frag_volume), _pf(rand),
+                                     i64(len(rand)))
+    fragmentation_limiters(n_fragment, frag_volume, vmin, nfmax, x_plus_y)
+
+
+def straub_fragmentation(n_fragment, CW, gam, ds, frag_volume, v_max, x_plus_y, rand, vmin,
+                         nfmax, Nr1, Nr2, Nr3, Nr4, Nrt, d34):
+    lib().oracle_straub_fragmentation(_pf(CW), _pf(gam), _pf(ds), _pf(v_max), _pf(frag_volume),
+                                      _pf(rand), _pf(Nr1), _pf(Nr2), _pf(Nr3), _pf(Nr4),
+                                      _pf(Nrt), _pf(d34), i64(len(rand)))
+    fragmentation_limiters(n_fragment, frag_volume, vmin, nfmax, x_plus_y)
+
+
+def ll82_fragmentation(n_fragment, CKE, W, W2, St, ds, dl, dcoal, frag_volume, x_plus_y, rand,
+                       vmin, nfmax, Rf, Rs, Rd, tol=1e-8):
+    lib().oracle_ll82_fragmentation(_pf(CKE), _pf(W), _pf(W2), _pf(St), _pf(ds), _pf(dl),
+                                    _pf(dcoal), _pf(frag_volume), _pf(rand), _pf(Rf), _pf(Rs),
+                                    _pf(Rd), i64(len(rand)), f64(tol))
+    fragmentation_limiters(n_fragment, frag_volume, vmin, nfmax, x_plus_y)
+
+
+def ll82_coalescence_check(Ec, dl):
+    lib().oracle_ll82_coalescence_check(_pf(Ec), _pf(dl), i64(len(Ec)))

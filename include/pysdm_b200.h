@@ -204,6 +204,90 @@ typedef struct pysdm_b200_fused_args {
 int64_t pysdm_b200_fused_max_cell_size(void);
 int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *host_args, void *stream);
 
+/* ---- terminal velocities: methods/terminal_velocity_methods.py ----------------------- */
+
+/* interpolation, terminal_velocity_methods.py:13-30 (Gunn-Kinzer table lookup,
+ * PySDM/dynamics/terminal_velocity/gunn_and_kinzer.py:108-133): b, c = tables f64[601] */
+int pysdm_b200_interpolation(double *output, const double *radius, int64_t n, double factor,
+                             const double *b, const double *c, void *stream);
+
+/* terminal_velocity, :32-44 with PySDM/physics/terminal_velocity/rogers_yau.py:13-23 */
+int pysdm_b200_terminal_velocity_rogers_yau(double *values, const double *radius, int64_t n,
+                                            double small_k, double medium_k, double large_k,
+                                            double small_r_limit, double medium_r_limit,
+                                            void *stream);
+
+/* power_series, :46-64; num_terms <= 8, coefficient arrays on the HOST */
+int pysdm_b200_power_series(double *values, const double *radius, int64_t n, int64_t num_terms,
+                            const double *host_prefactors, const double *host_powers,
+                            void *stream);
+
+/* linear_collection_efficiency, methods/collisions_methods.py:743-782.  host_params13 =
+ * (A, B, D1, D2, E1, E2, F1, F2, G1, G2, G3, Mf, Mg); bit e of int_mask set = params[e] was
+ * passed as an integer (Numba lowers `x ** int` as square-and-multiply, `x ** float` as pow:
+ * Hydrodynamic passes Mf = 4 and Mg = 8 as ints, collision_kernels/hydrodynamic.py:11-13). */
+int pysdm_b200_linear_collection_efficiency(const double *host_params13, int64_t int_mask,
+                                            double *output, int64_t out_len,
+                                            const double *radii, const uint8_t *is_first_in_pair,
+                                            const int64_t *idx, int64_t length, double unit,
+                                            void *stream);
+
+/* ---- breakup fragmentation functions: methods/fragmentation_methods.py ------------------
+ * Every entry point = the function body + fragmentation_limiters (:78-95) in one launch,
+ * as the reference's public methods do.  has_nfmax = 0 encodes `nfmax is None`. */
+
+/* slams_fragmentation, :106-133 */
+int pysdm_b200_slams_fragmentation(double *n_fragment, double *frag_volume,
+                                   const double *x_plus_y, double *probs, const double *rand,
+                                   int64_t n, double vmin, int has_nfmax, double nfmax,
+                                   void *stream);
+/* exp_fragmentation, :136-170 */
+int pysdm_b200_exp_fragmentation(double *n_fragment, double scale, double *frag_volume,
+                                 const double *x_plus_y, const double *rand, int64_t n,
+                                 double vmin, int has_nfmax, double nfmax, double tol,
+                                 void *stream);
+/* feingold1988_fragmentation, :172-198, 486-497; PySDM/physics/fragmentation_function/feingold1988.py */
+int pysdm_b200_feingold1988_fragmentation(double *n_fragment, double scale, double *frag_volume,
+                                          const double *x_plus_y, const double *rand, int64_t n,
+                                          double fragtol, double vmin, int has_nfmax,
+                                          double nfmax, void *stream);
+/* gauss_fragmentation, :200-216, 474-483 */
+int pysdm_b200_gauss_fragmentation(double *n_fragment, double mu, double sigma,
+                                   double *frag_volume, const double *x_plus_y,
+                                   const double *rand, int64_t n, double vmin, int has_nfmax,
+                                   double nfmax, void *stream);
+/* straub_fragmentation, :12-50, 218-260, 321-378; PySDM/physics/fragmentation_function/straub2010nf.py.
+ * Nr1..Nr3 are read-modify-write (the caller zero-fills them), Nr4, Nrt, d34 are outputs. */
+int pysdm_b200_straub_fragmentation(double *n_fragment, const double *CW, const double *gam,
+                                    const double *ds, double *frag_volume, const double *v_max,
+                                    const double *x_plus_y, const double *rand, double *Nr1,
+                                    double *Nr2, double *Nr3, double *Nr4, double *Nrt,
+                                    double *d34, int64_t n, double vmin, int has_nfmax,
+                                    double nfmax, void *stream);
+/* ll82_fragmentation, :52-74, 262-303, 380-472; PySDM/physics/fragmentation_function/lowlist82.py.
+ * rand is rescaled in place, as in the reference. */
+int pysdm_b200_ll82_fragmentation(double *n_fragment, const double *CKE, const double *W,
+                                  const double *W2, const double *St, const double *ds,
+                                  const double *dl, const double *dcoal, double *frag_volume,
+                                  const double *x_plus_y, double *rand, double *Rf, double *Rs,
+                                  double *Rd, int64_t n, double tol, double vmin, int has_nfmax,
+                                  double nfmax, void *stream);
+/* ll82_coalescence_check, :305-319 */
+int pysdm_b200_ll82_coalescence_check(double *Ec, const double *dl, int64_t n, void *stream);
+
+/* ---- collision_coalescence_breakup, methods/collisions_methods.py:62-311, 479-520 ------
+ * handle_all_breakups selects break_up_while (:178-243) over break_up (:135-175), as
+ * Formulae(handle_all_breakups=...) does.  n_overflow (device int64[1], may be NULL) is
+ * incremented once per pair that raised the overflow flag; the host prints the reference's
+ * warning when warn_overflows is set. */
+int pysdm_b200_collision_coalescence_breakup(
+    int64_t *multiplicity, const int64_t *idx, int64_t length, double *attributes,
+    int64_t n_attr, int64_t n_sd, const double *gamma, const double *rand, const double *Ec,
+    const double *Eb, const double *fragment_mass, int64_t *healthy, const int64_t *cell_id,
+    int64_t *coalescence_rate, int64_t *breakup_rate, int64_t *breakup_rate_deficit,
+    const uint8_t *is_first_in_pair, double max_multiplicity, const double *particle_mass,
+    int handle_all_breakups, int64_t *n_overflow, void *stream);
+
 /* PYSDM_B200_H_END_OF_METHOD_LEVEL -- fused step and later additions follow */
 
 #ifdef __cplusplus

@@ -570,6 +570,9 @@ static inline int break_up_while(i64 i, i64 j, i64 k, i64 cid, i64 *multiplicity
                                             fragment_mass[i], max_multiplicity, &take_from_j,
                                             &new_mult_k, &g, &overflow_flag);
             gamma_j_k = (double)g;
+            /* the reference loops forever when no transfer is possible (g == 0 changes
+             * nothing); both the oracle and the CUDA kernel leave the loop instead */
+            if (g == 0) break;
         }
         get_new_multiplicities_and_update_attributes(j, k, attributes, n_attr, n_sd, multiplicity,
                                                      take_from_j, new_mult_k, &nj, &nk);

@@ -54,6 +54,21 @@ SIGNATURES = {
     "pysdm_b200_max_cell_size": (INT, (P, I64, P, P, P)),
     "pysdm_b200_fused_max_cell_size": (I64, ()),
     "pysdm_b200_fused_collision_step": (INT, (P, P)),
+    "pysdm_b200_interpolation": (INT, (P, P, I64, F64, P, P, P)),
+    "pysdm_b200_terminal_velocity_rogers_yau": (INT, (P, P, I64, F64, F64, F64, F64, F64, P)),
+    "pysdm_b200_power_series": (INT, (P, P, I64, I64, P, P, P)),
+    "pysdm_b200_linear_collection_efficiency": (INT, (P, I64, P, I64, P, P, P, I64, F64, P)),
+    "pysdm_b200_slams_fragmentation": (INT, (P, P, P, P, P, I64, F64, INT, F64, P)),
+    "pysdm_b200_exp_fragmentation": (INT, (P, F64, P, P, P, I64, F64, INT, F64, F64, P)),
+    "pysdm_b200_feingold1988_fragmentation": (
+        INT, (P, F64, P, P, P, I64, F64, F64, INT, F64, P)),
+    "pysdm_b200_gauss_fragmentation": (INT, (P, F64, F64, P, P, P, I64, F64, INT, F64, P)),
+    "pysdm_b200_straub_fragmentation": (
+        INT, (P,) * 14 + (I64, F64, INT, F64, P)),
+    "pysdm_b200_ll82_fragmentation": (INT, (P,) * 14 + (I64, F64, F64, INT, F64, P)),
+    "pysdm_b200_ll82_coalescence_check": (INT, (P, P, I64, P)),
+    "pysdm_b200_collision_coalescence_breakup": (
+        INT, (P, P, I64, P, I64, I64) + (P,) * 11 + (F64, P, INT, P, P)),
 }
 
 

@@ -174,6 +174,101 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
                                 gamma.data, healthy.data, cell_id.data, coalescence_rate.data,
                                 is_first_in_pair.indicator.data)
 
+    def collision_coalescence_breakup(self, *, multiplicity, idx, attributes, gamma, rand, Ec,
+                                      Eb, fragment_mass, healthy, cell_id, coalescence_rate,
+                                      breakup_rate, breakup_rate_deficit, is_first_in_pair,
+                                      warn_overflows, particle_mass, max_multiplicity):
+        # :479-520 (body :246-311; break_up :135-175 or break_up_while :178-243)
+        n_overflow = m.collision_coalescence_breakup(
+            multiplicity.data, idx.data, len(idx), attributes.data, gamma.data, rand.data,
+            Ec.data, Eb.data, fragment_mass.data, healthy.data, cell_id.data,
+            coalescence_rate.data, breakup_rate.data, breakup_rate_deficit.data,
+            is_first_in_pair.indicator.data, max_multiplicity, particle_mass.data,
+            handle_all_breakups=bool(self.formulae.handle_all_breakups),
+            count_overflows=bool(warn_overflows))
+        if warn_overflows and n_overflow:
+            # impl_numba/warnings.py:12-21: the reference prints one message per pair from
+            # inside the kernel; here one message carries the count
+            import sys  # pylint: disable=import-outside-toplevel
+
+            print(f"overflow ({n_overflow} pairs)\n\tfile: {__file__}"
+                  "\n\tcontext:  collision_coalescence_breakup", file=sys.stderr)
+
+    def linear_collection_efficiency(self, *, params, output, radii, is_first_in_pair, unit):
+        # :743-782
+        m.linear_collection_efficiency(params, m.int_mask_of(params), output.data, radii.data,
+                                       is_first_in_pair.indicator.data, radii.idx.data,
+                                       len(is_first_in_pair), unit)
+
+    # ---- terminal velocities (terminal_velocity_methods.py) ---------------------------------
+    @staticmethod
+    def interpolation(*, output, radius, factor, b, c):  # :13-30
+        m.interpolation(output.data, radius.data, factor, b.data, c.data)
+
+    def terminal_velocity(self, *, values, radius):  # :32-44, values/radius are raw .data
+        name = type(self.formulae.terminal_velocity).__name__
+        if name != "RogersYau":
+            raise NotImplementedError(f"terminal_velocity formula {name}")
+        c = self.formulae.constants
+        m.terminal_velocity_rogers_yau(
+            values, radius,
+            (c.ROGERS_YAU_TERM_VEL_SMALL_K, c.ROGERS_YAU_TERM_VEL_MEDIUM_K,
+             c.ROGERS_YAU_TERM_VEL_LARGE_K, c.ROGERS_YAU_TERM_VEL_SMALL_R_LIMIT,
+             c.ROGERS_YAU_TERM_VEL_MEDIUM_R_LIMIT))
+
+    @staticmethod
+    def power_series(*, values, radius, num_terms, prefactors, powers):  # :46-64
+        m.power_series(values, radius, list(prefactors)[:num_terms], list(powers)[:num_terms])
+
+    # ---- fragmentation functions (fragmentation_methods.py) ---------------------------------
+    @staticmethod
+    def slams_fragmentation(n_fragment, frag_volume, x_plus_y, probs, rand, vmin, nfmax):
+        m.slams_fragmentation(n_fragment.data, frag_volume.data, x_plus_y.data, probs.data,
+                              rand.data, vmin, nfmax)  # :106-133
+
+    @staticmethod
+    def exp_fragmentation(*, n_fragment, scale, frag_volume, x_plus_y, rand, vmin, nfmax,
+                          tol=1e-5):  # :136-170
+        m.exp_fragmentation(n_fragment.data, scale, frag_volume.data, x_plus_y.data, rand.data,
+                            vmin, nfmax, tol)
+
+    def feingold1988_fragmentation(self, *, n_fragment, scale, frag_volume, x_plus_y, rand,
+                                   fragtol, vmin, nfmax):  # :172-198
+        self._need_fragmentation_function("Feingold1988")
+        m.feingold1988_fragmentation(n_fragment.data, scale, frag_volume.data, x_plus_y.data,
+                                     rand.data, fragtol, vmin, nfmax)
+
+    @staticmethod
+    def gauss_fragmentation(*, n_fragment, mu, sigma, frag_volume, x_plus_y, rand, vmin, nfmax):
+        m.gauss_fragmentation(n_fragment.data, mu, sigma, frag_volume.data, x_plus_y.data,
+                              rand.data, vmin, nfmax)  # :200-216
+
+    def straub_fragmentation(self, *, n_fragment, CW, gam, ds, frag_volume, v_max, x_plus_y,
+                             rand, vmin, nfmax, Nr1, Nr2, Nr3, Nr4, Nrt, d34):  # :218-260
+        self._need_fragmentation_function("Straub2010Nf")
+        m.straub_fragmentation(n_fragment.data, CW.data, gam.data, ds.data, frag_volume.data,
+                               v_max.data, x_plus_y.data, rand.data, vmin, nfmax, Nr1.data,
+                               Nr2.data, Nr3.data, Nr4.data, Nrt.data, d34.data)
+
+    def ll82_fragmentation(self, *, n_fragment, CKE, W, W2, St, ds, dl, dcoal, frag_volume,
+                           x_plus_y, rand, vmin, nfmax, Rf, Rs, Rd, tol=1e-8):  # :262-303
+        self._need_fragmentation_function("LowList1982Nf")
+        m.ll82_fragmentation(n_fragment.data, CKE.data, W.data, W2.data, St.data, ds.data,
+                             dl.data, dcoal.data, frag_volume.data, x_plus_y.data, rand.data,
+                             vmin, nfmax, Rf.data, Rs.data, Rd.data, tol)
+
+    @staticmethod
+    def ll82_coalescence_check(*, Ec, dl):  # :305-319
+        m.ll82_coalescence_check(Ec.data, dl.data)
+
+    def _need_fragmentation_function(self, name):
+        """the reference reaches these formulae through Formulae(fragmentation_function=name)
+        and fails at JIT time otherwise; fail the same way, early"""
+        have = type(self.formulae.fragmentation_function).__name__
+        if have != name:
+            raise AttributeError(
+                f"Formulae(fragmentation_function='{name}') required (got '{have}')")
+
     # ---- physics (physics_methods.py:107-133) -----------------------------------------------
     def volume_of_water_mass(self, volume, mass):
         m.volume_of_water_mass(volume.data, mass.data, self.rho_w)

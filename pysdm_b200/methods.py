@@ -262,3 +262,119 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         kernel_b=float(kernel_b), kernel=_lib.KERNELS[kernel], reserved=0,
         max_cell_size=int(max_cell), nf_slot=_pf(nf_slot), refresh_nf=int(bool(refresh_nf)))
     return _lib.load().pysdm_b200_fused_collision_step(ctypes.byref(args), _stream())
+
+
+# ---- terminal velocities, collection efficiency (csrc/physics.cu) ---------------------------
+def _host_f64(values):
+    """small host-side parameter arrays (kept alive by the caller's frame during the call)"""
+    arr = (ctypes.c_double * len(values))(*[float(v) for v in values])
+    return arr
+
+
+def interpolation(output, radius, factor, b, c):
+    check(_lib.load().pysdm_b200_interpolation(_pf(output), _pf(radius), radius.numel(),
+                                               float(factor), _pf(b), _pf(c), _stream()),
+          "interpolation")
+
+
+def terminal_velocity_rogers_yau(values, radius, params):
+    """params = (small_k, medium_k, large_k, small_r_limit, medium_r_limit)"""
+    check(_lib.load().pysdm_b200_terminal_velocity_rogers_yau(
+        _pf(values), _pf(radius), values.numel(), *[float(p) for p in params], _stream()),
+        "terminal_velocity")
+
+
+def power_series(values, radius, prefactors, powers):
+    pre, pw = _host_f64(prefactors), _host_f64(powers)
+    check(_lib.load().pysdm_b200_power_series(_pf(values), _pf(radius), values.numel(), len(pw),
+                                              pre, pw, _stream()), "power_series")
+
+
+def int_mask_of(params):
+    """bit e set when params[e] is an integer (include/pysdm_b200.h)"""
+    import numbers  # pylint: disable=import-outside-toplevel
+
+    return sum(1 << e for e, v in enumerate(params)
+               if isinstance(v, numbers.Integral) and not isinstance(v, bool))
+
+
+def linear_collection_efficiency(params, int_mask, output, radii, is_first_in_pair, idx, length,
+                                 unit):
+    par = _host_f64(params)
+    assert len(par) == 13
+    check(_lib.load().pysdm_b200_linear_collection_efficiency(
+        par, int(int_mask), _pf(output), output.numel(), _pf(radii), _pb(is_first_in_pair),
+        _pi(idx), int(length), float(unit), _stream()), "linear_collection_efficiency")
+
+
+# ---- fragmentation functions (csrc/physics.cu) ---------------------------------------------
+def _lim(vmin, nfmax):
+    return float(vmin), int(nfmax is not None), float(0.0 if nfmax is None else nfmax)
+
+
+def slams_fragmentation(n_fragment, frag_volume, x_plus_y, probs, rand, vmin, nfmax):
+    check(_lib.load().pysdm_b200_slams_fragmentation(
+        _pf(n_fragment), _pf(frag_volume), _pf(x_plus_y), _pf(probs), _pf(rand), rand.numel(),
+        *_lim(vmin, nfmax), _stream()), "slams_fragmentation")
+
+
+def exp_fragmentation(n_fragment, scale, frag_volume, x_plus_y, rand, vmin, nfmax, tol=1e-5):
+    check(_lib.load().pysdm_b200_exp_fragmentation(
+        _pf(n_fragment), float(scale), _pf(frag_volume), _pf(x_plus_y), _pf(rand), rand.numel(),
+        *_lim(vmin, nfmax), float(tol), _stream()), "exp_fragmentation")
+
+
+def feingold1988_fragmentation(n_fragment, scale, frag_volume, x_plus_y, rand, fragtol, vmin,
+                               nfmax):
+    check(_lib.load().pysdm_b200_feingold1988_fragmentation(
+        _pf(n_fragment), float(scale), _pf(frag_volume), _pf(x_plus_y), _pf(rand), rand.numel(),
+        float(fragtol), *_lim(vmin, nfmax), _stream()), "feingold1988_fragmentation")
+
+
+def gauss_fragmentation(n_fragment, mu, sigma, frag_volume, x_plus_y, rand, vmin, nfmax):
+    check(_lib.load().pysdm_b200_gauss_fragmentation(
+        _pf(n_fragment), float(mu), float(sigma), _pf(frag_volume), _pf(x_plus_y), _pf(rand),
+        rand.numel(), *_lim(vmin, nfmax), _stream()), "gauss_fragmentation")
+
+
+def straub_fragmentation(n_fragment, CW, gam, ds, frag_volume, v_max, x_plus_y, rand, vmin,
+                         nfmax, Nr1, Nr2, Nr3, Nr4, Nrt, d34):
+    check(_lib.load().pysdm_b200_straub_fragmentation(
+        _pf(n_fragment), _pf(CW), _pf(gam), _pf(ds), _pf(frag_volume), _pf(v_max), _pf(x_plus_y),
+        _pf(rand), _pf(Nr1), _pf(Nr2), _pf(Nr3), _pf(Nr4), _pf(Nrt), _pf(d34), rand.numel(),
+        *_lim(vmin, nfmax), _stream()), "straub_fragmentation")
+
+
+def ll82_fragmentation(n_fragment, CKE, W, W2, St, ds, dl, dcoal, frag_volume, x_plus_y, rand,
+                       vmin, nfmax, Rf, Rs, Rd, tol=1e-8):
+    check(_lib.load().pysdm_b200_ll82_fragmentation(
+        _pf(n_fragment), _pf(CKE), _pf(W), _pf(W2), _pf(St), _pf(ds), _pf(dl), _pf(dcoal),
+        _pf(frag_volume), _pf(x_plus_y), _pf(rand), _pf(Rf), _pf(Rs), _pf(Rd), rand.numel(),
+        float(tol), *_lim(vmin, nfmax), _stream()), "ll82_fragmentation")
+
+
+def ll82_coalescence_check(Ec, dl):
+    check(_lib.load().pysdm_b200_ll82_coalescence_check(_pf(Ec), _pf(dl), Ec.numel(), _stream()),
+          "ll82_coalescence_check")
+
+
+# ---- breakup (csrc/breakup.cu) -----------------------------------------------------------------
+def collision_coalescence_breakup(multiplicity, idx, length, attributes, gamma, rand, Ec, Eb,
+                                  fragment_mass, healthy, cell_id_, coalescence_rate,
+                                  breakup_rate, breakup_rate_deficit, is_first_in_pair,
+                                  max_multiplicity, particle_mass, handle_all_breakups=False,
+                                  count_overflows=False):
+    """returns the number of pairs that raised the overflow flag when `count_overflows`
+    (synchronises), else None"""
+    n_attr, n_sd = attributes.shape
+    counter = None
+    if count_overflows:
+        counter = torch.zeros(1, dtype=torch.int64, device=multiplicity.device)
+    check(_lib.load().pysdm_b200_collision_coalescence_breakup(
+        _pi(multiplicity), _pi(idx), int(length), _pf(attributes), n_attr, n_sd, _pf(gamma),
+        _pf(rand), _pf(Ec), _pf(Eb), _pf(fragment_mass), _pi(healthy), _pi(cell_id_),
+        _pi(coalescence_rate), _pi(breakup_rate), _pi(breakup_rate_deficit),
+        _pb(is_first_in_pair), float(max_multiplicity), _pf(particle_mass),
+        int(bool(handle_all_breakups)), _pi(counter), _stream()),
+        "collision_coalescence_breakup")
+    return int(counter.item()) if count_overflows else None

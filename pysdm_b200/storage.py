@@ -305,8 +305,30 @@ class Storage(StorageBase):
     def fill(self, other):
         if isinstance(other, Storage):
             self.data[:] = other.data
+        elif isinstance(other, np.ndarray):
+            self.upload(other)
+        elif other is None:  # numpy semantics of `float_array[:] = None`
+            self.data[:] = float("nan")
         else:
             self.data[:] = other
+
+    # ---- numpy interoperability -----------------------------------------------------------
+    # The reference's orchestration applies numpy ufuncs to Storage objects in one place
+    # (`output.fill(np.exp(We))`, dynamics/collisions/coalescence_efficiencies/straub2010.py);
+    # with the Numba backend numpy walks the Storage through the sequence protocol.  Here
+    # np.exp stays on the device (own kernel) and returns a Storage; any other ufunc gets a
+    # host copy through __array__.
+    def __array_ufunc__(self, ufunc, method, *inputs, **kwargs):
+        if ufunc is np.exp and method == "__call__" and len(inputs) == 1 and not kwargs:
+            out = Storage.empty(self.shape, self.dtype)
+            out._ew("exp", None, self.data)  # pylint: disable=protected-access
+            return out
+        arrays = [i.to_ndarray() if isinstance(i, Storage) else i for i in inputs]
+        return getattr(ufunc, method)(*arrays, **kwargs)
+
+    def __array__(self, dtype=None, copy=None):  # pylint: disable=unused-argument
+        host = self.to_ndarray()
+        return host if dtype is None else host.astype(dtype)
 
 
 def host_int_result():

@@ -151,3 +151,110 @@ def scale_prob_for_adaptive_sdm_gamma(prob, idx, length, multiplicity, cell_id_,
     dev.scale_prob_for_adaptive_sdm_gamma(d[0], d[1], length, d[2], d[3], d[4], dt, dt_range,
                                           d[5], d[6], d[7])
     m.back(0, 4, 6, 7)
+
+
+# ---- physics rows (tests/test_physics_golden.py) ---------------------------------------------
+def power(x, exponent):
+    m = _Mirror(x)
+    dev.elementwise("pow", m.dev[0], a=m.dev[0], scalar=exponent)
+    m.back(0)
+
+
+def product_scalar(out, in_, scalar):
+    m = _Mirror(out, in_)
+    dev.elementwise("mul", m.dev[0], a=m.dev[1], scalar=scalar)
+    m.back(0)
+
+
+def interpolation(output, radius, factor, b, c):
+    m = _Mirror(output, radius, b, c)
+    dev.interpolation(m.dev[0], m.dev[1], factor, m.dev[2], m.dev[3])
+    m.back(0)
+
+
+def terminal_velocity_rogers_yau(values, radius, params):
+    m = _Mirror(values, radius)
+    dev.terminal_velocity_rogers_yau(m.dev[0], m.dev[1], params)
+    m.back(0)
+
+
+def power_series(values, radius, prefactors, powers):
+    m = _Mirror(values, radius)
+    dev.power_series(m.dev[0], m.dev[1], prefactors, powers)
+    m.back(0)
+
+
+def linear_collection_efficiency(params, int_mask, output, radii, is_first_in_pair, idx, length,
+                                 unit):
+    m = _Mirror(output, radii, is_first_in_pair, idx)
+    dev.linear_collection_efficiency(params, int_mask, m.dev[0], m.dev[1], m.dev[2], m.dev[3],
+                                     length, unit)
+    m.back(0)
+
+
+def slams_fragmentation(n_fragment, frag_volume, x_plus_y, probs, rand, vmin, nfmax):
+    m = _Mirror(n_fragment, frag_volume, x_plus_y, probs, rand)
+    dev.slams_fragmentation(*m.dev, vmin, nfmax)
+    m.back(0, 1, 3)
+
+
+def exp_fragmentation(n_fragment, scale, frag_volume, x_plus_y, rand, vmin, nfmax, tol=1e-5):
+    m = _Mirror(n_fragment, frag_volume, x_plus_y, rand)
+    d = m.dev
+    dev.exp_fragmentation(d[0], scale, d[1], d[2], d[3], vmin, nfmax, tol)
+    m.back(0, 1)
+
+
+def feingold1988_fragmentation(n_fragment, scale, frag_volume, x_plus_y, rand, fragtol, vmin,
+                               nfmax):
+    m = _Mirror(n_fragment, frag_volume, x_plus_y, rand)
+    d = m.dev
+    dev.feingold1988_fragmentation(d[0], scale, d[1], d[2], d[3], fragtol, vmin, nfmax)
+    m.back(0, 1)
+
+
+def gauss_fragmentation(n_fragment, mu, sigma, frag_volume, x_plus_y, rand, vmin, nfmax):
+    m = _Mirror(n_fragment, frag_volume, x_plus_y, rand)
+    d = m.dev
+    dev.gauss_fragmentation(d[0], mu, sigma, d[1], d[2], d[3], vmin, nfmax)
+    m.back(0, 1)
+
+
+def straub_fragmentation(n_fragment, CW, gam, ds, frag_volume, v_max, x_plus_y, rand, vmin,
+                         nfmax, Nr1, Nr2, Nr3, Nr4, Nrt, d34):
+    m = _Mirror(n_fragment, CW, gam, ds, frag_volume, v_max, x_plus_y, rand, Nr1, Nr2, Nr3, Nr4,
+                Nrt, d34)
+    d = m.dev
+    dev.straub_fragmentation(*d[:8], vmin, nfmax, *d[8:])
+    m.back(0, 4, 8, 9, 10, 11, 12, 13)
+
+
+def ll82_fragmentation(n_fragment, CKE, W, W2, St, ds, dl, dcoal, frag_volume, x_plus_y, rand,
+                       vmin, nfmax, Rf, Rs, Rd, tol=1e-8):
+    m = _Mirror(n_fragment, CKE, W, W2, St, ds, dl, dcoal, frag_volume, x_plus_y, rand, Rf, Rs,
+                Rd)
+    d = m.dev
+    dev.ll82_fragmentation(*d[:11], vmin, nfmax, *d[11:], tol)
+    m.back(0, 8, 10, 11, 12, 13)
+
+
+def ll82_coalescence_check(Ec, dl):
+    m = _Mirror(Ec, dl)
+    dev.ll82_coalescence_check(*m.dev)
+    m.back(0)
+
+
+def collision_coalescence_breakup(multiplicity, idx, length, attributes, gamma, rand, Ec, Eb,
+                                  fragment_mass, healthy, cell_id_, coalescence_rate,
+                                  breakup_rate, breakup_rate_deficit, is_first_in_pair,
+                                  max_multiplicity, particle_mass, handle_all_breakups=False):
+    m = _Mirror(multiplicity, idx, attributes, gamma, rand, Ec, Eb, fragment_mass, healthy,
+                cell_id_, coalescence_rate, breakup_rate, breakup_rate_deficit,
+                is_first_in_pair, particle_mass)
+    d = m.dev
+    n = dev.collision_coalescence_breakup(d[0], d[1], length, d[2], d[3], d[4], d[5], d[6], d[7],
+                                          d[8], d[9], d[10], d[11], d[12], d[13],
+                                          max_multiplicity, d[14], handle_all_breakups,
+                                          count_overflows=True)
+    m.back(0, 2, 8, 10, 11, 12)
+    return n

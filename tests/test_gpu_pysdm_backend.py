@@ -131,3 +131,140 @@ def test_b200_backend_equals_numba_backend(pysdm, case):
             np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
         collided = int(b["coalescence_rate"].sum())
     assert collided > 0
+
+
+# ---- configs 2 and 3 of BASELINE.json in miniature: gravitational kernels with hydrodynamic
+# efficiency, adaptive time step, breakup with the fragmentation functions ---------------------
+def build_physics(pysdm, backend, *, n_sd, dv, dt, attributes, dynamic):
+    from PySDM import Builder  # pylint: disable=import-outside-toplevel
+    from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
+
+    builder = Builder(n_sd=n_sd, backend=backend, environment=Box(dv=dv, dt=dt))
+    builder.add_dynamic(dynamic())
+    return builder.build(attributes={k: np.array(v) for k, v in attributes.items()}, products=())
+
+
+def _dynamics(name):
+    # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics import Coalescence, Collision
+    from PySDM.dynamics.collisions.breakup_efficiencies import ConstEb
+    from PySDM.dynamics.collisions.breakup_fragmentations import (AlwaysN, Exponential,
+                                                                  Feingold1988, Gaussian,
+                                                                  LowList1982Nf, SLAMS,
+                                                                  Straub2010Nf)
+    from PySDM.dynamics.collisions.coalescence_efficiencies import (Berry1967, ConstEc,
+                                                                    LowList1982Ec, Straub2010Ec)
+    from PySDM.dynamics.collisions.collision_kernels import Geometric, Hydrodynamic
+    from PySDM.physics import si
+
+    vmin = (0.01 * si.mm) ** 3 * np.pi / 6
+    return {
+        # config 2: Berry 1967 box
+        "hydrodynamic_adaptive": lambda: Coalescence(
+            collision_kernel=Hydrodynamic(), adaptive=True, dt_coal_range=(0.1, 100.0)),
+        "geometric": lambda: Coalescence(collision_kernel=Geometric(), adaptive=False),
+        # config 3: de Jong et al. breakup box
+        "breakup_straub": lambda: Collision(
+            collision_kernel=Geometric(), coalescence_efficiency=Straub2010Ec(),
+            breakup_efficiency=ConstEb(1.0),
+            fragmentation_function=Straub2010Nf(vmin=vmin, nfmax=10000), adaptive=True,
+            warn_overflows=False),
+        "breakup_berry_straub": lambda: Collision(
+            collision_kernel=Geometric(), coalescence_efficiency=Berry1967(),
+            breakup_efficiency=ConstEb(1.0),
+            fragmentation_function=Straub2010Nf(vmin=vmin, nfmax=10000), adaptive=True,
+            warn_overflows=False),
+        "breakup_ll82": lambda: Collision(
+            collision_kernel=Geometric(), coalescence_efficiency=LowList1982Ec(),
+            breakup_efficiency=ConstEb(1.0),
+            fragmentation_function=LowList1982Nf(vmin=vmin, nfmax=10000), adaptive=True,
+            warn_overflows=False),
+        "breakup_always_n": lambda: Collision(
+            collision_kernel=Geometric(), coalescence_efficiency=ConstEc(0.5),
+            breakup_efficiency=ConstEb(1.0), fragmentation_function=AlwaysN(n=4),
+            adaptive=False, warn_overflows=False),
+        "breakup_exponential": lambda: Collision(
+            collision_kernel=Geometric(), coalescence_efficiency=ConstEc(0.5),
+            breakup_efficiency=ConstEb(0.9),
+            fragmentation_function=Exponential(scale=4 / 3 * np.pi * (100 * si.um) ** 3,
+                                               vmin=vmin, nfmax=100),
+            adaptive=False, warn_overflows=False),
+        "breakup_gaussian": lambda: Collision(
+            collision_kernel=Geometric(), coalescence_efficiency=ConstEc(0.5),
+            breakup_efficiency=ConstEb(1.0),
+            fragmentation_function=Gaussian(mu=4 / 3 * np.pi * (100 * si.um) ** 3,
+                                            sigma=4 / 3 * np.pi * (50 * si.um) ** 3,
+                                            vmin=vmin, nfmax=100),
+            adaptive=False, warn_overflows=False),
+        "breakup_feingold": lambda: Collision(
+            collision_kernel=Geometric(), coalescence_efficiency=ConstEc(0.5),
+            breakup_efficiency=ConstEb(1.0),
+            fragmentation_function=Feingold1988(scale=4 / 3 * np.pi * (100 * si.um) ** 3,
+                                                fragtol=1e-3, vmin=vmin, nfmax=100),
+            adaptive=False, warn_overflows=False),
+        "breakup_slams": lambda: Collision(
+            collision_kernel=Geometric(), coalescence_efficiency=ConstEc(0.5),
+            breakup_efficiency=ConstEb(1.0), fragmentation_function=SLAMS(vmin=vmin, nfmax=100),
+            adaptive=False, warn_overflows=False),
+    }[name]
+
+
+FRAG_FUNCTION = {"breakup_straub": "Straub2010Nf", "breakup_berry_straub": "Straub2010Nf",
+                 "breakup_ll82": "LowList1982Nf", "breakup_feingold": "Feingold1988"}
+PHYSICS_CASES = ("hydrodynamic_adaptive", "geometric", "breakup_straub", "breakup_berry_straub",
+                 "breakup_ll82", "breakup_always_n", "breakup_exponential", "breakup_gaussian",
+                 "breakup_feingold", "breakup_slams")
+
+
+@pytest.mark.parametrize("case", PHYSICS_CASES)
+def test_b200_backend_physics_cases(pysdm, case):
+    """Same protocol as above for the gravitational kernels / breakup.  The collision
+    probability now goes through pow/exp/log of CUDA's libm, which is not bit-identical to
+    glibc's: multiplicities, pair flags, permutation, gamma and the rate counters must still
+    be identical (a difference would be an fp64 gamma within an ulp of an integer boundary,
+    north_star; it is counted and reported as the test failure), attributes to 1e-12."""
+    from PySDM import Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200  # pylint: disable=import-outside-toplevel
+
+    n_sd = 2048
+    rng = np.random.default_rng(7)
+    radius = rng.exponential(0.12e-3, n_sd) + 20e-6 if case.startswith("breakup") else \
+        rng.exponential(12e-6, n_sd) + 2e-6
+    attributes = {
+        "multiplicity": rng.integers(*((5, 200) if case.startswith("breakup") else (200, 4000)), n_sd).astype(np.int64),
+        "volume": 4 / 3 * np.pi * radius ** 3,
+    }
+    fkw = dict(fastmath=False, seed=4321)
+    if case in FRAG_FUNCTION:
+        fkw["fragmentation_function"] = FRAG_FUNCTION[case]
+    dv, dt = (1.0, 1.0) if case.startswith("breakup") else (0.05, 10.0)
+    common = dict(n_sd=n_sd, dv=dv, dt=dt, attributes=attributes, dynamic=_dynamics(case))
+    ref = build_physics(pysdm, CPU(Formulae(**fkw)), **common)
+    sut = build_physics(pysdm, B200(Formulae(**fkw), host_rng=True), **common)
+    events = 0
+    for step in range(6):
+        ref.run(1)
+        sut.run(1)
+        a, b = snapshot(sut), snapshot(ref)
+        n = b["length"]
+        assert a["length"] == n, f"step {step}: length"
+        np.testing.assert_array_equal(a["idx"][:n], b["idx"][:n], f"step {step}: idx")
+        np.testing.assert_array_equal(a["flag"][:n], b["flag"][:n], f"step {step}: flag")
+        flips = int((a["gamma"] != b["gamma"]).sum())
+        assert flips == 0, f"step {step}: {flips} gamma values differ (integer-boundary flips)"
+        np.testing.assert_array_equal(a["multiplicity"], b["multiplicity"], f"step {step}")
+        np.testing.assert_allclose(a["attributes"], b["attributes"], rtol=1e-12, atol=0,
+                                   err_msg=f"step {step}: attributes")
+        for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate",
+                  "stats_n_substep"):
+            np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
+        dyn_a, dyn_b = sut.dynamics["Collision"], ref.dynamics["Collision"]
+        if case.startswith("breakup"):
+            for k in ("breakup_rate", "breakup_rate_deficit"):
+                np.testing.assert_array_equal(getattr(dyn_a, k).to_ndarray(),
+                                              getattr(dyn_b, k).to_ndarray(), f"step {step}: {k}")
+            events += int(dyn_b.breakup_rate.to_ndarray().sum())
+        events += int(b["coalescence_rate"].sum())
+    assert events > 0

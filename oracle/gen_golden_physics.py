@@ -229,6 +229,10 @@ def gen_physics():
             gamma = rng.integers(0, 4, p).astype(np.float64)
             if not hab:  # (large gamma overflows -> break_up_while would not terminate)
                 gamma[rng.integers(0, p, p // 10)] = 25.0
+            # slots without a pair carry gamma = 0 in a real step (prob = 0 there, quirk A6);
+            # a nonzero gamma would make pair_indices hand out a droplet of the NEXT slot's pair
+            fl = flag.indicator.data
+            gamma[~(fl[0:2 * p:2] | fl[1:2 * p:2])] = 0.0
             rand_p = rng.uniform(0, 1, p)
             Ec_a = rng.uniform(0, 0.6, p)
             Eb_a = rng.uniform(0.5, 1.0, p)

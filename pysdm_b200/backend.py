@@ -264,7 +264,8 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
     def _need_fragmentation_function(self, name):
         """the reference reaches these formulae through Formulae(fragmentation_function=name)
         and fails at JIT time otherwise; fail the same way, early"""
-        have = type(self.formulae.fragmentation_function).__name__
+        frag = self.formulae.fragmentation_function  # SimpleNamespace named by _pick, formulae.py:371
+        have = getattr(frag, "__name__", type(frag).__name__)
         if have != name:
             raise AttributeError(
                 f"Formulae(fragmentation_function='{name}') required (got '{have}')")

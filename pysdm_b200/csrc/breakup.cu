@@ -7,6 +7,10 @@
 //   :178-243 break_up_while (Formulae(handle_all_breakups=True))
 //   :246-311 collision_coalescence_breakup body    :479-520 host wrapper
 //
+// `particle_mass` normally IS a row of `attributes` (the water-mass attribute,
+// particulator.py:179-209), so neither pointer is __restrict__: break_up_while re-reads the
+// masses the previous transfer wrote.
+//
 // One thread per pair slot; a super-droplet belongs to at most one pair, so threads never
 // touch each other's particles.  Rates go to per-cell int64 counters (warp-aggregated
 // atomics).  HBM traffic per pair: gamma, rand, Ec, Eb, fragment_mass (40 B) + for pairs
@@ -62,7 +66,7 @@ __device__ __forceinline__ Transfer compute_transfer(double gamma, double n_j, d
 
 // :96-114; returns the (float) new multiplicities through nj, nk
 __device__ __forceinline__ void new_multiplicities_and_attributes(
-    i64 j, i64 k, double *__restrict__ attributes, i64 n_attr, i64 n_sd, double n_j, double n_k,
+    i64 j, i64 k, double *attributes, i64 n_attr, i64 n_sd, double n_j, double n_k,
     double take_from_j, double new_mult_k, double &nj, double &nk)
 {
     const double recip = 1.0 / new_mult_k;
@@ -85,7 +89,7 @@ __device__ __forceinline__ void new_multiplicities_and_attributes(
 
 // :117-132
 __device__ __forceinline__ void round_multiplicities(i64 j, i64 k, double nj, double nk,
-                                                     double *__restrict__ attributes, i64 n_attr,
+                                                     double *attributes, i64 n_attr,
                                                      i64 n_sd, i64 *__restrict__ mult)
 {
     i64 rj = (i64)rint(nj), rk = (i64)rint(nk);
@@ -104,12 +108,12 @@ __device__ __forceinline__ void round_multiplicities(i64 j, i64 k, double nj, do
 template <bool HandleAll>
 __global__ void k_collision_coalescence_breakup(
     i64 *__restrict__ mult, const i64 *__restrict__ idx, i64 n_pairs,
-    double *__restrict__ attributes, i64 n_attr, i64 n_sd, const double *__restrict__ gamma,
+    double *attributes, i64 n_attr, i64 n_sd, const double *__restrict__ gamma,
     const double *__restrict__ rand, const double *__restrict__ Ec, const double *__restrict__ Eb,
     const double *__restrict__ fragment_mass, i64 *__restrict__ healthy,
     const i64 *__restrict__ cell_id, i64 *__restrict__ coalescence_rate,
     i64 *__restrict__ breakup_rate, i64 *__restrict__ breakup_rate_deficit,
-    const u8 *__restrict__ flag, double max_multiplicity, const double *__restrict__ particle_mass,
+    const u8 *__restrict__ flag, double max_multiplicity, const double *particle_mass,
     i64 *__restrict__ n_overflow)
 {
     const i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;

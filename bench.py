@@ -221,9 +221,8 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
     t_beg.record()
     for k in range(args.steps):
         ev[k][0].record()
-        sim.step_fused()     # the launch
-        ev[k][1].record()
-        sim.sanitize()       # `healthy` read-back each step, as the reference does
+        sim.step_async(mark=ev[k][1])  # the launch; `healthy` of step k-1 is read behind it
+    sim.drain()              # `healthy` of the last step (the reference reads it every step)
     t_end.record()
     barrier()
     clocks = sampler.summary()

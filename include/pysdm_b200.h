@@ -199,6 +199,13 @@ typedef struct pysdm_b200_fused_args {
     int64_t refresh_nf;         /* != 0: recompute norm_factor and nf_slot first.  Must be set
                                    whenever cell_start, cell_idx, cell_id, timestep or dv changed
                                    since the previous call with the same nf_slot buffer */
+    int64_t *gate;              /* [1] or NULL.  Lets the caller queue step k+1 before it has read
+                                   `healthy` of step k (the reference reads it after every step,
+                                   PySDM/impl/particle_attributes.py:67-73): a launch does nothing
+                                   at all when gate[0] is neither 0 nor `epoch`, and a launch that
+                                   clears healthy[0] stores its `epoch` in gate[0].  The caller
+                                   zeroes gate[0] when it has removed the zero-multiplicity SDs. */
+    int64_t epoch;              /* != 0, different for consecutive launches */
 } pysdm_b200_fused_args;
 
 int64_t pysdm_b200_fused_max_cell_size(void);

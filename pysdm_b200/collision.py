@@ -135,6 +135,11 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.n_fused_steps = 0
         self.n_launches = 0  # CUDA launches issued through the C-ABI (entry-point calls)
         self._healthy_host = torch.ones(1, dtype=i64).pin_memory()
+        # speculative stepping (step_async): gate word of the fused kernel, two pinned slots
+        # for the `healthy` flags in flight, the step whose flag has not been read yet
+        self.gate = full(1, 0, i64)
+        self._healthy_slots = torch.ones(2, dtype=i64).pin_memory()
+        self._pending = None
         # Builder.build: zero multiplicities are removed up front
         if bool((self.multiplicity == 0).any().item()):
             self.healthy.zero_()
@@ -166,11 +171,15 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
 
     def sanitize(self):
         if not self.is_healthy():
-            self.length = self.valid_n_sd
-            self.length = m.remove_zero_n_or_flagged(self.multiplicity, self.idx, self.length)
-            self.valid_n_sd = self.length
-            self.healthy.fill_(1)
-            self.sorted = False
+            self._remove_zero_multiplicities()
+
+    def _remove_zero_multiplicities(self):
+        self.length = self.valid_n_sd
+        self.length = m.remove_zero_n_or_flagged(self.multiplicity, self.idx, self.length)
+        self.valid_n_sd = self.length
+        self.healthy.fill_(1)
+        self.gate.zero_()
+        self.sorted = False
 
     def permutation(self, u01, local):
         if local:
@@ -214,8 +223,14 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.substep = 0
 
     def run(self, steps):
+        if self.adaptive or self.substeps != 1:
+            for _ in range(steps):
+                self()
+            return
         for _ in range(steps):
-            self()
+            self.step_async()
+            self.substep = 0
+        self.drain()
 
     def _fused_ok(self):
         if self.fused is False or self.adaptive or self.croupier != "local":
@@ -237,7 +252,52 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             self.step_methods()
         self.sanitize()
 
-    def step_fused(self):
+    # ---- speculative stepping: no host wait between fused launches ---------------------------
+    def step_async(self, mark=None):
+        """`step()` without the GPU idling while the host reads `healthy` (the reference reads
+        it after every step, impl/particle_attributes.py:67-73): the fused launch of this step
+        is queued first, then the flag of the PREVIOUS step is read.  If that step left zero
+        multiplicities, the launch just queued found its gate closed and did nothing
+        (pysdm_b200.h `gate`): its host bookkeeping is undone, the dead super-droplets are
+        removed and the step is issued again -- same results as step(), step by step.
+        Needs the device Philox generator (its stream position can be rewound); otherwise,
+        and whenever the fused step does not apply, this is step().  Call drain() before
+        reading state.  `mark`: a CUDA event recorded right behind the fused launch (timing)."""
+        if not isinstance(self.rnd, Random) or not self._fused_ok():
+            self.drain()
+            self.step()
+            if mark is not None:
+                mark.record()
+            return
+        self.step_fused(gated=True)
+        if mark is not None:
+            mark.record()
+        slot = 0 if self._pending is None else 1 - self._pending[1]
+        self._healthy_slots[slot:slot + 1].copy_(self.healthy, non_blocking=True)
+        event = torch.cuda.Event()
+        event.record()
+        previous, self._pending = self._pending, (event, slot)
+        if previous is not None and not self._resolved_healthy(previous):
+            # undo the bookkeeping of the launch that did nothing, then redo the step
+            self.idx, self.tmp_idx = self.tmp_idx, self.idx
+            self.rnd.call -= 2
+            self.n_fused_steps -= 1
+            self._pending = None
+            self._remove_zero_multiplicities()
+            self.step_async(mark)
+
+    def _resolved_healthy(self, pending):
+        event, slot = pending
+        event.synchronize()
+        return bool(self._healthy_slots[slot])
+
+    def drain(self):
+        """waits for the step in flight and sanitizes after it, as step() would have"""
+        pending, self._pending = self._pending, None
+        if pending is not None and not self._resolved_healthy(pending):
+            self._remove_zero_multiplicities()
+
+    def step_fused(self, gated=False):
         """one launch: csrc/fused.cu"""
         kw = {}
         if isinstance(self.rnd, Random):  # uniforms generated in-kernel from the same stream
@@ -256,7 +316,8 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             length=self.length, max_cell=self.max_cell, kernel=self.kernel.fused,
             kernel_a=self.kernel.a, kernel_b=self.kernel.b, timestep=self.dt, dv=self.dv,
             rho_w=self.rho_w, substeps=self.substeps, nf_slot=self.nf_slot,
-            refresh_nf=not self.nf_valid, **kw)
+            refresh_nf=not self.nf_valid, gate=self.gate if gated else None,
+            epoch=self.n_fused_steps + 1, **kw)
         m.check(err, "fused_collision_step")
         self.n_launches += 1 if self.nf_valid else 3
         self.nf_valid = True

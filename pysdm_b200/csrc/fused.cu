@@ -223,7 +223,10 @@ __device__ __forceinline__ void process_hits(const FusedArgs &a, u32 pf, double 
                 row[sk] = v;
                 if (!keep) row[sj] = v;
             }
-            if (nj_new == 0 || nk_new == 0) a.healthy[0] = 0;
+            if (nj_new == 0 || nk_new == 0) {
+                a.healthy[0] = 0;
+                if (a.gate) a.gate[0] = a.epoch;
+            }
         }
     }
     counter_add<kAggregate>(a.collision_rate, cid, add_rate, active);
@@ -241,7 +244,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     const int gt = kWarp ? (tid & 31) : tid;  // thread number within the group
     unsigned char *smem = smem_all + group * G::kBytes;
     u32 *sd = reinterpret_cast<u32 *>(smem);
-    u16 *jl = reinterpret_cast<u16 *>(smem + G::kSd);
+    u16 *jl = reinterpret_cast<u16 *>(smem + G::kSd);  // swap targets as byte offsets into sd
     u8 *cellof = smem + G::kSd + G::kJl;
     i32 *cs = reinterpret_cast<i32 *>(smem + G::kSd + G::kJl + G::kCo);
     double *fd = reinterpret_cast<double *>(smem + G::kSd + G::kJl + G::kCo + G::kCs);
@@ -253,6 +256,12 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     u32 *q_pf = reinterpret_cast<u32 *>(qbase + 64 * 8);
     int qn = 0;  // warp-uniform fill level
 
+    // a previous launch left zero multiplicities behind and the caller has not removed them
+    // yet: this step was queued speculatively and must not happen (pysdm_b200.h, `gate`)
+    if (a.gate) {
+        const i64 g = *(volatile const i64 *)a.gate;
+        if (g != 0 && g != a.epoch) return;
+    }
     const i64 n_pairs_active = a.length / 2;
     // literal chain for a slot without a pair: max_pair -> 0; *= kernel_temp; normalize
     const double prob_nopair = 0.0 * kernel_temp_of<K>(0.0, a.kernel_a, a.kernel_b);
@@ -308,81 +317,99 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     const int n_iter = (P + 4 * G::kSize - 1) / (4 * G::kSize);
 
     // ---- phase 2: stream idx + uniforms in, stage SD numbers and swap targets -------------
+    // kFast: every window of the batch (also the padding up to a whole number of window
+    // groups) lies inside the arrays and is 16-byte aligned, so the loads are unconditional
+    // and the loads of kWin windows are issued together, ahead of the Philox work, to have
+    // kWin * 512 B per warp in flight (the exposed idx latency was 19 % of the warp time,
+    // profiles/r1h); validity is applied when staging.  Otherwise: guarded scalar loads.
     {
         const i64 *idx_b = a.idx_in + base_al;  // batch-local bases: 32-bit offsets below
         const double *u01_b = kPhilox ? nullptr : a.u01 + base_al;
         const u64 blk_b = (u64)base_al >> 1;    // Philox block of local position 0
-        const bool vec_idx = (((uintptr_t)a.idx_in) & 15) == 0;
-        const bool vec_u = !kPhilox && (((uintptr_t)a.u01) & 15) == 0;
-#pragma unroll 2
-        for (int it = 0; it < n_iter; ++it) {
-            i64 sv[2][2];
-            double uv[2][2];
+        constexpr int kWin = 4;                 // windows (of 2 * kSize positions) per group
+        const int n_win = 2 * n_iter;           // window w covers lp = 2*kSize*w + 2*gt, +1
+        const int n_grp = (n_win + kWin - 1) / kWin;
+        const bool fast = (((uintptr_t)a.idx_in) & 15) == 0 &&
+                          (kPhilox || (((uintptr_t)a.u01) & 15) == 0) &&
+                          base_al + (i64)n_grp * kWin * 2 * G::kSize <= a.n_sd;
+        auto stage = [&](int lp0, i64 s0, i64 s1, double u0, double u1) {
+            const i64 svq[2] = {s0, s1};
+            const double uvq[2] = {u0, u1};
+            u32 jrel[2] = {0, 0};
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int lp0 = 4 * G::kSize * it + 2 * G::kSize * h + 2 * gt;
-                const bool v0 = lp0 >= lo && lp0 < P, v1 = lp0 + 1 < P;
-                sv[h][0] = sv[h][1] = 0;
-                uv[h][0] = uv[h][1] = 0.0;
-                if (v0 && v1 && vec_idx) {
-                    const longlong2 t = *reinterpret_cast<const longlong2 *>(idx_b + (u32)lp0);
-                    sv[h][0] = t.x;
-                    sv[h][1] = t.y;
-                } else {
-                    if (v0) sv[h][0] = idx_b[(u32)lp0];
-                    if (v1) sv[h][1] = idx_b[(u32)lp0 + 1];
+            for (int q = 0; q < 2; ++q) {
+                const int lp = lp0 + q;
+                if (lp < lo || lp >= P) continue;
+                const int c = cellof[lp];
+                const int s = cs[c], len = cs[c + 1] - s;
+                // index_methods.py:40: j = int(cell_start[c] + u01[i] * (cell_end - cell_start));
+                // 0 <= x < 2^33: floor by a round-down add, integer in the low mantissa bits
+                const double x = fd[2 * c] + uvq[q] * fd[2 * c + 1];
+                const double t = __dadd_rd(x, kTwo52);
+                // j < 2^33: low word minus the low word of the cell's global start is exact
+                int jr = (int)((u32)__double2loint(t) - (u32)(base_al + s));
+                if (jr >= len) jr = len - 1;  // fp round-up at huge cell_start (see index.cu)
+                jrel[q] = 4u * (u32)phys(s + jr);  // byte offset of the swap target in sd[]
+            }
+            if (lp0 >= lo && lp0 + 1 < P) {
+                const int ph = phys(lp0);
+                *reinterpret_cast<uint2 *>(sd + ph) = make_uint2((u32)svq[0], (u32)svq[1]);
+                *reinterpret_cast<u32 *>(jl + ph) = jrel[0] | (jrel[1] << 16);
+            } else {
+                if (lp0 >= lo && lp0 < P) {
+                    sd[phys(lp0)] = (u32)svq[0];
+                    jl[phys(lp0)] = (u16)jrel[0];
                 }
-                if (kPhilox) {
-                    if (lp0 < P) {
-                        u32 w[4];
-                        const u64 b = blk_b + (u32)(lp0 >> 1);  // block = elements 2b, 2b + 1
-                        philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_u01,
-                                      (u32)(a.call_u01 >> 32), (u32)a.seed, (u32)(a.seed >> 32), w);
-                        uv[h][0] = u01_from_words(w[0], w[1]);
-                        uv[h][1] = u01_from_words(w[2], w[3]);
-                    }
-                } else if (v0 && v1 && vec_u) {
-                    const double2 t = *reinterpret_cast<const double2 *>(u01_b + (u32)lp0);
-                    uv[h][0] = t.x;
-                    uv[h][1] = t.y;
-                } else {
-                    if (v0) uv[h][0] = u01_b[(u32)lp0];
-                    if (v1) uv[h][1] = u01_b[(u32)lp0 + 1];
+                if (lp0 + 1 >= lo && lp0 + 1 < P) {
+                    sd[phys(lp0 + 1)] = (u32)svq[1];
+                    jl[phys(lp0 + 1)] = (u16)jrel[1];
                 }
             }
+        };
+        auto philox_pair = [&](int lp0, double &u0, double &u1) {
+            u32 w[4];
+            const u64 b = blk_b + (u32)(lp0 >> 1);  // block = elements 2b, 2b + 1
+            philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_u01, (u32)(a.call_u01 >> 32),
+                          (u32)a.seed, (u32)(a.seed >> 32), w);
+            u0 = u01_from_words(w[0], w[1]);
+            u1 = u01_from_words(w[2], w[3]);
+        };
+        if (fast) {
+            for (int g = 0; g < n_grp; ++g) {
+                longlong2 sv[kWin];
+                double2 uv[kWin];
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int lp0 = 4 * G::kSize * it + 2 * G::kSize * h + 2 * gt;
-                u32 jrel[2] = {0, 0};
-#pragma unroll
-                for (int q = 0; q < 2; ++q) {
-                    const int lp = lp0 + q;
-                    if (lp < lo || lp >= P) continue;
-                    const int c = cellof[lp];
-                    const int s = cs[c], len = cs[c + 1] - s;
-                    // index_methods.py:40: j = int(cell_start[c] + u01[i] * (cell_end - cell_start));
-                    // 0 <= x < 2^33: floor by a round-down add, integer in the low mantissa bits
-                    const double x = fd[2 * c] + uv[h][q] * fd[2 * c + 1];
-                    const double t = __dadd_rd(x, kTwo52);
-                    // j < 2^33: low word minus the low word of the cell's global start is exact
-                    int jr = (int)((u32)__double2loint(t) - (u32)(base_al + s));
-                    if (jr >= len) jr = len - 1;  // fp round-up at huge cell_start (see index.cu)
-                    jrel[q] = (u32)phys(s + jr);  // skewed smem index of the swap target
+                for (int w = 0; w < kWin; ++w) {
+                    const int lp0 = 2 * G::kSize * (g * kWin + w) + 2 * gt;
+                    sv[w] = *reinterpret_cast<const longlong2 *>(idx_b + (u32)lp0);
+                    if (!kPhilox) uv[w] = *reinterpret_cast<const double2 *>(u01_b + (u32)lp0);
                 }
-                if (lp0 >= lo && lp0 + 1 < P) {
-                    const int ph = phys(lp0);
-                    *reinterpret_cast<uint2 *>(sd + ph) = make_uint2((u32)sv[h][0], (u32)sv[h][1]);
-                    *reinterpret_cast<u32 *>(jl + ph) = jrel[0] | (jrel[1] << 16);
+#pragma unroll
+                for (int w = 0; w < kWin; ++w) {
+                    const int lp0 = 2 * G::kSize * (g * kWin + w) + 2 * gt;
+                    if (kPhilox && lp0 < P) philox_pair(lp0, uv[w].x, uv[w].y);
+                }
+#pragma unroll
+                for (int w = 0; w < kWin; ++w) {
+                    const int lp0 = 2 * G::kSize * (g * kWin + w) + 2 * gt;
+                    if (lp0 < P) stage(lp0, sv[w].x, sv[w].y, uv[w].x, uv[w].y);
+                }
+            }
+        } else {
+            for (int w = 0; w < n_win; ++w) {
+                const int lp0 = 2 * G::kSize * w + 2 * gt;
+                const bool v0 = lp0 >= lo && lp0 < P, v1 = lp0 + 1 < P;
+                i64 s0 = 0, s1 = 0;
+                double u0 = 0.0, u1 = 0.0;
+                if (v0) s0 = idx_b[(u32)lp0];
+                if (v1) s1 = idx_b[(u32)lp0 + 1];
+                if (kPhilox) {
+                    if (lp0 < P) philox_pair(lp0, u0, u1);
                 } else {
-                    if (lp0 >= lo && lp0 < P) {
-                        sd[phys(lp0)] = (u32)sv[h][0];
-                        jl[phys(lp0)] = (u16)jrel[0];
-                    }
-                    if (lp0 + 1 >= lo && lp0 + 1 < P) {
-                        sd[phys(lp0 + 1)] = (u32)sv[h][1];
-                        jl[phys(lp0 + 1)] = (u16)jrel[1];
-                    }
+                    if (v0) u0 = u01_b[(u32)lp0];
+                    if (v1) u1 = u01_b[(u32)lp0 + 1];
                 }
+                if (lp0 < P) stage(lp0, s0, s1, u0, u1);
             }
         }
     }
@@ -393,13 +420,23 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
         const int s = cs[c], e = cs[c + 1];
         i64 cid = 0;
         if (e > s) cid = a.cell_id[sd[phys(s)]];  // issued now, consumed after the chain
-        int pi = phys(e - 1);
-        for (int i = e - 1; i > s; --i) {
-            const int pj = jl[pi];
-            const u32 x = sd[pi], y = sd[pj];
-            sd[pi] = y;
-            sd[pj] = x;
-            pi -= (i & 63) ? 1 : 3;  // phys(i - 1): two pad slots at every multiple of 64
+        // positions of a 64-block are contiguous in the skewed layout: walk block by block
+        // with unit stride (the bookkeeping of the skew was half of the chain's instructions)
+        int i = e - 1;
+        while (i > s) {
+            const int blk = i & ~63;
+            const int lowest = blk > s ? blk : s + 1;  // last position handled in this block
+            const int n = i - lowest + 1;
+            u32 *psd = sd + phys(i);
+            const u16 *pjl = jl + phys(i);
+#pragma unroll 4
+            for (int t = 0; t < n; ++t) {
+                u32 *q = reinterpret_cast<u32 *>(reinterpret_cast<unsigned char *>(sd) + pjl[-t]);
+                const u32 x = psd[-t], y = *q;
+                psd[-t] = y;
+                *q = x;
+            }
+            i = lowest - 1;
         }
         cidv[c] = cid;
     }
@@ -418,26 +455,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     const i64 dl_left = n_pairs_active - (base_al >> 1);  // slots below go through compute_gamma
     const int dl_active = dl_left > (i64)G::kPos ? G::kPos : (dl_left < 0 ? 0 : (int)dl_left);
     for (int it = 0; it < n_iter; ++it) {  // uniform trip count: warp-collective code inside
-        // uniforms of this warp's 2 x 32 slots: 32 Philox blocks, one per lane (block b holds
-        // elements 2b, 2b + 1); lane x gets slot (h, x) from lane 16h + x/2
         double rnd[2] = {0.0, 0.0};
-        if (kPhilox) {
-            const int lane = tid & 31, wig = (gt >> 5) << 5;  // first thread of my warp in group
-            // local slot (even) whose block this lane computes; global slot = base_al/2 + it
-            const int dl_mine = 2 * G::kSize * it + G::kSize * (lane >> 4) + wig + 2 * (lane & 15);
-            u32 w[4];
-            const u64 b = ((u64)base_al >> 2) + (u32)(dl_mine >> 1);
-            philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_rand, (u32)(a.call_rand >> 32),
-                          (u32)a.seed, (u32)(a.seed >> 32), w);
-            const double r0 = u01_from_words(w[0], w[1]), r1 = u01_from_words(w[2], w[3]);
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int src = 16 * h + (lane >> 1);
-                const double e0 = __shfl_sync(0xffffffffu, r0, src);
-                const double e1 = __shfl_sync(0xffffffffu, r1, src);
-                rnd[h] = (lane & 1) ? e1 : e0;
-            }
-        }
 
         // stage A: find_pairs (pair_methods.py:38-41, :55) for my positions, pair members
         bool has[2], dflt[2];
@@ -516,6 +534,27 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
                     mk[h] = mass[k[h]];
                 }
             }
+
+        // uniforms of this warp's 2 x 32 slots: 32 Philox blocks, one per lane (block b holds
+        // elements 2b, 2b + 1); lane x gets slot (h, x) from lane 16h + x/2
+        if (kPhilox) {
+            const int lane = tid & 31, wig = (gt >> 5) << 5;  // first thread of my warp in group
+            // local slot (even) whose block this lane computes; global slot = base_al/2 + it
+            const int dl_mine = 2 * G::kSize * it + G::kSize * (lane >> 4) + wig + 2 * (lane & 15);
+            u32 w[4];
+            const u64 b = ((u64)base_al >> 2) + (u32)(dl_mine >> 1);
+            philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_rand, (u32)(a.call_rand >> 32),
+                          (u32)a.seed, (u32)(a.seed >> 32), w);
+            const double r0 = u01_from_words(w[0], w[1]), r1 = u01_from_words(w[2], w[3]);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int src = 16 * h + (lane >> 1);
+                const double e0 = __shfl_sync(0xffffffffu, r0, src);
+                const double e1 = __shfl_sync(0xffffffffu, r1, src);
+                rnd[h] = (lane & 1) ? e1 : e0;
+            }
+        }
+        // (issued after the gathers above so that the Philox arithmetic overlaps their latency)
 
         // stage B: sort within pair, probability, gamma.  Pairs that do collide (gamma != 0, a
         // few per cent) are queued per warp and handled with full lanes by process_hits()

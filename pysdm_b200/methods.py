@@ -244,7 +244,7 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
                          collision_rate_deficit, coalescence_rate, healthy, status, length,
                          max_cell, kernel, kernel_a=0.0, kernel_b=0.0, timestep, dv, rho_w,
                          substeps=1, mass_row=0, u01=None, rand=None, seed=0, call_u01=0,
-                         call_rand=0, nf_slot, refresh_nf=True):
+                         call_rand=0, nf_slot, refresh_nf=True, gate=None, epoch=1):
     """one Collision.step() in one launch; returns the CUDA error code (9 = a cell is
     larger than the fused path supports -> use the method-level functions)"""
     n_attr, n_sd = attributes.shape
@@ -260,7 +260,8 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         call_u01=int(call_u01), call_rand=int(call_rand), timestep=float(timestep),
         dv=float(dv), rho_w=float(rho_w), substeps=float(substeps), kernel_a=float(kernel_a),
         kernel_b=float(kernel_b), kernel=_lib.KERNELS[kernel], reserved=0,
-        max_cell_size=int(max_cell), nf_slot=_pf(nf_slot), refresh_nf=int(bool(refresh_nf)))
+        max_cell_size=int(max_cell), nf_slot=_pf(nf_slot), refresh_nf=int(bool(refresh_nf)),
+        gate=_pi(gate), epoch=int(epoch))
     return _lib.load().pysdm_b200_fused_collision_step(ctypes.byref(args), _stream())
 
 

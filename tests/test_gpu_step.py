@@ -145,6 +145,25 @@ def test_fused_philox_equals_methods_philox():
     assert sims[0].host("coalescence_rate").sum() > 0
 
 
+def test_speculative_stepping_equals_step_by_step():
+    """run() queues fused step k+1 before reading `healthy` of step k (gate word of the fused
+    kernel); small multiplicities make steps leave zero-multiplicity SDs, so the gate closes,
+    the queued launch must do nothing and be redone after the removal: the final state has to
+    equal the one of step-by-step execution (which test_fused_philox_equals_methods_philox
+    pins to the method-level path)"""
+    pop = ragged_population(seed=9, n_cell=400, mean=90, n_attr=2, max_mult=2)
+    sims = [device_sim(kernel=device_kernel(b=GOLOVIN_B), dt=1.0, dv=1e-7, seed=12, fused=True,
+                       **pop) for _ in range(2)]
+    lengths = set()
+    for _ in range(8):
+        sims[0]()
+        lengths.add(sims[0].length)
+    sims[1].run(8)
+    assert len(lengths) > 2, "super-droplets were expected to be removed in several steps"
+    assert sims[1].n_fused_steps == 8 and sims[1].n_launches > sims[0].n_launches
+    compare_states(sims[1], _Host(sims[0]), "speculative vs step by step")
+
+
 class _Host:  # pylint: disable=too-few-public-methods
     """numpy face of a DeviceCollision, shaped like OracleCollision for compare_states"""
 

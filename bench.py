@@ -47,7 +47,8 @@ def parse():
                     help="bounded CPU sample: super-droplets per CPU step (log2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--e2e-stripes", type=int, default=4)
     return ap.parse_args()
 
 
@@ -238,7 +239,9 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
     # ---- e2e: host buffers in, host buffers out, every step (see DESIGN.md "measurement") ----
     e2e = None
     if not args.no_e2e:
-        e2e = e2e_run(args, sim, pop, world, barrier)
+        del sim
+        torch.cuda.empty_cache()
+        e2e = e2e_run(args, pop, rank, world, barrier)
     peak, peak_src = hbm_peak()
     achieved = BYTES_PER_SD * n_sd / (kernel_ms * 1e-3) / 1e9
     line = {
@@ -268,45 +271,30 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
         dist.destroy_process_group()
 
 
-def e2e_run(args, sim, pop, world, barrier):
-    """the same metric through the public step API with HOST buffers: every step uploads the
-    super-droplet state (multiplicity, water mass, cell id) from pinned host memory, runs
-    sort-by-cell + the collision step, and reads multiplicity, water mass and the
-    coalescence counter back to pinned host memory"""
+def e2e_run(args, pop, rank, world, barrier):
+    """the same metric through the host-facing API (pysdm_b200.host_step.HostCollisionStep):
+    every step uploads the super-droplet state (multiplicity, water mass, cell id) from pinned
+    host memory, runs sort-by-cell + the collision step, and reads multiplicity, water mass
+    and the coalescence counters back to pinned host memory; cells are cut into stripes so
+    that upload, compute and download of different stripes overlap"""
     import torch  # pylint: disable=import-outside-toplevel
     import torch.distributed as dist  # pylint: disable=import-outside-toplevel
 
-    from pysdm_b200 import methods as m  # pylint: disable=import-outside-toplevel
+    from pysdm_b200.collision import Golovin  # pylint: disable=import-outside-toplevel
+    from pysdm_b200.host_step import HostCollisionStep  # pylint: disable=import-outside-toplevel
 
-    h_mult = torch.from_numpy(pop["multiplicity"]).pin_memory()
-    h_mass = torch.from_numpy(pop["water_mass"]).reshape(1, -1).pin_memory()
-    h_cid = torch.from_numpy(pop["cell_id"]).pin_memory()
-    o_mult = torch.empty_like(h_mult).pin_memory()
-    o_mass = torch.empty_like(h_mass).pin_memory()
-    o_rate = torch.empty(sim.n_cell, dtype=torch.int64).pin_memory()
-    h2d = h_mult.numel() * 8 + h_mass.numel() * 8 + h_cid.numel() * 8
-    d2h = o_mult.numel() * 8 + o_mass.numel() * 8 + o_rate.numel() * 8
-
-    def one_step():
-        sim.multiplicity.copy_(h_mult, non_blocking=True)
-        sim.attributes.copy_(h_mass, non_blocking=True)
-        sim.cell_id.copy_(h_cid, non_blocking=True)
-        m.identity_index(sim.idx)
-        sim.length = sim.valid_n_sd = sim.n_sd
-        sim.sorted = False
-        sim.step()
-        o_mult.copy_(sim.multiplicity, non_blocking=True)
-        o_mass.copy_(sim.attributes, non_blocking=True)
-        o_rate.copy_(sim.coalescence_rate, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-
+    host = HostCollisionStep(
+        multiplicity=pop["multiplicity"], attributes=pop["water_mass"].reshape(1, -1),
+        cell_id=pop["cell_id"], n_cell=pop["n_cell"], n_stripes=args.e2e_stripes,
+        seed=1000 * (rank + 1), kernel=Golovin(GOLOVIN_B), dt=1.0, dv=1.0, fused=True)
     for _ in range(3):
-        one_step()
+        host.step()
+    launches0 = host.n_launches
     beg, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     beg.record()
     for _ in range(args.e2e_steps):
-        one_step()
+        host.step()
     end.record()
     barrier()
     ms = beg.elapsed_time(end)
@@ -314,10 +302,13 @@ def e2e_run(args, sim, pop, world, barrier):
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    return {"value": world * sim.n_sd * args.e2e_steps / (ms * 1e-3), "unit": "SD-steps/s",
-            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
-            "ms_per_step": ms / args.e2e_steps,
-            "what": "pinned host state -> H2D -> sort by cell + fused collision step -> D2H"}
+    n_sd = host.n_sd
+    return {"value": world * n_sd * args.e2e_steps / (ms * 1e-3), "unit": "SD-steps/s",
+            "h2d_bytes_per_step": host.h2d_bytes, "d2h_bytes_per_step": host.d2h_bytes,
+            "steps": args.e2e_steps, "ms_per_step": ms / args.e2e_steps,
+            "gpu_launches": host.n_launches - launches0, "stripes": len(host.stripes),
+            "what": "HostCollisionStep: pinned host state -> H2D -> sort by cell + fused "
+                    "collision step -> D2H, cells in stripes over 3 streams"}
 
 
 def main():

@@ -159,6 +159,19 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.max_cell = None
         self.nf_valid = False
 
+    def reset_permutation(self):
+        """after the caller has overwritten multiplicity / attributes / cell_id in place:
+        identity permutation over all super-droplets, cell order to be rebuilt
+        (ParticleAttributes.__init__ + recalculate_cell_id, impl/particle_attributes.py:24-40,98-105)"""
+        self.drain()
+        m.identity_index(self.idx)
+        self.length = self.valid_n_sd = self.n_sd
+        self.sorted = False
+        self.n_launches += 1
+        if bool((self.multiplicity == 0).any().item()):  # as Builder.build does up front
+            self.healthy.zero_()
+            self.sanitize()
+
     def get_cell_start(self):
         if not self.sorted:
             self.sort_by_cell_id()

@@ -44,6 +44,9 @@ enum { KERNEL_GOLOVIN = 0, KERNEL_CONSTANT_K = 1, KERNEL_LINEAR = 2 };
 #ifndef PYSDM_WARP_POS
 #define PYSDM_WARP_POS 1024
 #endif
+#ifndef PYSDM_KWIN
+#define PYSDM_KWIN 4  // phase 2: windows of idx loads in flight per thread
+#endif
 #ifndef PYSDM_MIN_CTAS
 #define PYSDM_MIN_CTAS 3
 #endif
@@ -326,7 +329,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
         const i64 *idx_b = a.idx_in + base_al;  // batch-local bases: 32-bit offsets below
         const double *u01_b = kPhilox ? nullptr : a.u01 + base_al;
         const u64 blk_b = (u64)base_al >> 1;    // Philox block of local position 0
-        constexpr int kWin = 4;                 // windows (of 2 * kSize positions) per group
+        constexpr int kWin = PYSDM_KWIN;  // windows (of 2 * kSize positions) per group
         const int n_win = 2 * n_iter;           // window w covers lp = 2*kSize*w + 2*gt, +1
         const int n_grp = (n_win + kWin - 1) / kWin;
         const bool fast = (((uintptr_t)a.idx_in) & 15) == 0 &&

@@ -164,6 +164,45 @@ def test_speculative_stepping_equals_step_by_step():
     compare_states(sims[1], _Host(sims[0]), "speculative vs step by step")
 
 
+def test_host_step_stripes_equal_separate_runs():
+    """HostCollisionStep (host arrays in/out, cells cut into stripes, three streams) gives what
+    the stripes give when run one after another as plain DeviceCollisions"""
+    from pysdm_b200.host_step import HostCollisionStep  # pylint: disable=import-outside-toplevel
+    from pysdm_b200.sharding import shard_population  # pylint: disable=import-outside-toplevel
+
+    pop = ragged_population(seed=10, n_cell=333, mean=70, n_attr=2)
+    order = np.argsort(pop["cell_id"], kind="stable")
+    mult, cid = pop["multiplicity"][order], pop["cell_id"][order]
+    attrs = np.stack([pop["water_mass"][order]] + [e[order] for e in pop["extra_attributes"]])
+    kw = dict(dt=1.0, dv=2e-7)
+    n_stripes, steps = 3, 3
+    host = HostCollisionStep(multiplicity=mult, attributes=attrs, cell_id=cid, n_cell=333,
+                             n_stripes=n_stripes, seed=21, kernel=device_kernel(b=GOLOVIN_B), **kw)
+    refs = []
+    for s in range(n_stripes):
+        n_s, a_s, c_s, n_cell_s, mine = shard_population(mult, attrs, cid, 333, s, n_stripes)
+        refs.append((device_sim(multiplicity=n_s, water_mass=a_s[0], extra_attributes=[a_s[1]],
+                                cell_id=c_s, n_cell=n_cell_s, seed=21 + s,
+                                kernel=device_kernel(b=GOLOVIN_B), **kw), mine))
+    for step in range(steps):
+        host.step()
+        for sim, mine in refs:
+            if step:
+                sim.reset_permutation()
+            sim()
+            np.testing.assert_array_equal(host.out_multiplicity.numpy()[mine],
+                                          sim.host("multiplicity"), f"step {step}")
+            assert_same_f64(host.out_attributes.numpy()[:, mine], sim.host("attributes"),
+                            f"step {step} attributes")
+        # the host model carries the state on: outputs become the next step's inputs
+        host.multiplicity.copy_(host.out_multiplicity)
+        host.attributes.copy_(host.out_attributes)
+    rate = host.out_coalescence_rate.numpy()
+    np.testing.assert_array_equal(rate, np.concatenate([s.host("coalescence_rate")
+                                                        for s, _ in refs]))
+    assert rate.sum() > 0 and host.h2d_bytes == mult.size * 8 * 4
+
+
 class _Host:  # pylint: disable=too-few-public-methods
     """numpy face of a DeviceCollision, shaped like OracleCollision for compare_states"""
 

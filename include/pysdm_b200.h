@@ -295,6 +295,62 @@ int pysdm_b200_collision_coalescence_breakup(
     const uint8_t *is_first_in_pair, double max_multiplicity, const double *particle_mass,
     int handle_all_breakups, int64_t *n_overflow, void *stream);
 
+/* ---- rows either side of the collision step -------------------------------- */
+
+/* Storage operators used by Displacement.update_cell_origin / boundary_condition
+ * (PySDM/dynamics/displacement.py:141-153) on mixed int64 / fp64 storages:
+ * `int_storage.floor(float_storage)`, `float_storage -= int_storage`,
+ * `int_storage %= int_divisors` (impl_numba/storage.py:54-100, storage_impl.py:11-83) */
+int pysdm_b200_floor_to_i64(int64_t *out, const double *in, int64_t n, void *stream);
+int pysdm_b200_sub_i64(double *inout, const int64_t *b, int64_t n, void *stream);
+int pysdm_b200_row_modulo_i64(int64_t *out, const int64_t *divisor, int64_t n_rows,
+                              int64_t n_cols, void *stream);
+
+/* moments, methods/moments_methods.py:12-98.  moment_0 f64[n_cell], moments f64[n_ranks, n_cell]
+ * (both zero-filled first, as the reference does); host_ranks = the `ranks` storage on the
+ * HOST, n_ranks <= PYSDM_B200_MAX_MOMENT_RANKS; *_is_int != 0 = the exponent was passed as a
+ * Python int (Numba then multiplies instead of calling pow).  Sums are fp64 atomics:
+ * within 1e-12 relative of the reference's serial sums, not bit-identical. */
+#define PYSDM_B200_MAX_MOMENT_RANKS 16
+int pysdm_b200_moments(double *moment_0, double *moments, const int64_t *multiplicity,
+                       const double *attr_data, const int64_t *cell_id, const int64_t *idx,
+                       int64_t length, const double *host_ranks, int64_t n_ranks, double min_x,
+                       double max_x, const double *x_attr, const double *weighting_attribute,
+                       double weighting_rank, int weighting_rank_is_int, int skip_division_by_m0,
+                       int64_t n_cell, void *stream);
+/* spectrum_moments, methods/moments_methods.py:100-182.  moment_0, moments f64[n_bins, n_cell],
+ * x_bins f64[n_bins + 1] on the device */
+int pysdm_b200_spectrum_moments(double *moment_0, double *moments, const int64_t *multiplicity,
+                                const double *attr_data, const int64_t *cell_id,
+                                const int64_t *idx, int64_t length, double rank, int rank_is_int,
+                                const double *x_bins, int64_t n_bins, const double *x_attr,
+                                const double *weighting_attribute, double weighting_rank,
+                                int weighting_rank_is_int, int64_t n_cell, void *stream);
+
+/* calculate_displacement, methods/displacement_methods.py:14-153: one call per `dim`, as
+ * Particulator.calculate_displacement issues them (particulator.py:428-440).  courant = the
+ * component `dim` of the Courant field on the Arakawa-C grid, row-major, shape
+ * host_courant_shape[n_dims] (HOST array); cell_origin i64[n_dims, n_sd], position_in_cell and
+ * displacement f64[n_dims, n_sd]; implicit_in_space selects
+ * PySDM/physics/particle_advection/implicit_in_space.py over explicit_in_space.py */
+int pysdm_b200_calculate_displacement(int dim, int n_dims, int implicit_in_space,
+                                      double *displacement, const double *courant,
+                                      const int64_t *host_courant_shape,
+                                      const int64_t *cell_origin, const double *position_in_cell,
+                                      int64_t n_sd, double n_substeps, void *stream);
+/* flag_precipitated, :155-186, 208-238: the *_z pointers are the LAST rows of the [n_dims, n_sd]
+ * arrays; flagged positions of idx get idx_len (= n_sd); rainfall_mass = device f64[1] */
+int pysdm_b200_flag_precipitated(const int64_t *cell_origin_z, const double *position_in_cell_z,
+                                 const double *water_mass, const int64_t *multiplicity,
+                                 int64_t *idx, int64_t length, int64_t idx_len, int64_t *healthy,
+                                 double precipitation_counting_level_index,
+                                 const double *displacement_z, double *rainfall_mass,
+                                 void *stream);
+/* flag_out_of_column, :188-206, 240-260 */
+int pysdm_b200_flag_out_of_column(const int64_t *cell_origin_z, const double *position_in_cell_z,
+                                  int64_t *idx, int64_t length, int64_t idx_len,
+                                  int64_t *healthy, double domain_top_level_index, void *stream);
+
 /* PYSDM_B200_H_END_OF_METHOD_LEVEL -- fused step and later additions follow */
 
 #ifdef __cplusplus

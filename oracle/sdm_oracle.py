@@ -23,7 +23,8 @@ ptr = ctypes.c_void_p
 
 def build(force=False):
     """compile the C restatement with the system gcc (seconds)"""
-    srcs = [os.path.join(_HERE, f) for f in ("sdm_oracle.c", "sdm_physics.c", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("sdm_oracle.c", "sdm_physics.c", "sdm_transport.c",
+                                             "Makefile")]
     if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(map(os.path.getmtime, srcs)):
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
     return _SO
@@ -40,6 +41,7 @@ def lib():
         _lib.oracle_remove_zero_n_or_flagged.restype = i64
         _lib.oracle_adaptive_sdm_end.restype = i64
         _lib.oracle_collision_coalescence_breakup.restype = i64
+        _lib.oracle_flag_precipitated.restype = f64
     return _lib
 
 
@@ -293,3 +295,63 @@ def ll82_fragmentation(n_fragment, CKE, W, W2, St, ds, dl, dcoal, frag_volume, x
 
 def ll82_coalescence_check(Ec, dl):
     lib().oracle_ll82_coalescence_check(_pf(Ec), _pf(dl), i64(len(Ec)))
+
+
+# ---- products and transport side (oracle/sdm_transport.c) ---------------------------------------
+def _is_int(x):
+    return int(isinstance(x, (int, np.integer)) and not isinstance(x, bool))
+
+
+def moments(moment_0, moments_, multiplicity, attr_data, cell_id_, idx, length, ranks, min_x,
+            max_x, x_attr, weighting_attribute, weighting_rank, skip_division_by_m0):
+    ranks = np.ascontiguousarray(ranks, dtype=np.float64)
+    lib().oracle_moments(
+        _p(moment_0), _p(moments_), _p(multiplicity), _p(attr_data) if len(ranks) else None,
+        _p(cell_id_), _p(idx), i64(length), _p(ranks), i64(len(ranks)), f64(min_x), f64(max_x),
+        _p(x_attr), _p(weighting_attribute), f64(weighting_rank),
+        ctypes.c_int(_is_int(weighting_rank)), ctypes.c_int(int(bool(skip_division_by_m0))),
+        i64(len(moment_0)))
+
+
+def spectrum_moments(moment_0, moments_, multiplicity, attr_data, cell_id_, idx, length, rank,
+                     x_bins, x_attr, weighting_attribute, weighting_rank):
+    n_bins, n_cell = moments_.shape
+    lib().oracle_spectrum_moments(
+        _p(moment_0), _p(moments_), _p(multiplicity), _p(attr_data), _p(cell_id_), _p(idx),
+        i64(length), f64(rank), ctypes.c_int(_is_int(rank)), _p(x_bins), i64(n_bins), _p(x_attr),
+        _p(weighting_attribute), f64(weighting_rank), ctypes.c_int(_is_int(weighting_rank)),
+        i64(n_cell))
+
+
+def calculate_displacement(dim, displacement, courant, cell_origin, position_in_cell, n_substeps,
+                           implicit_in_space=True):
+    n_dims, n_sd = displacement.shape
+    shape = np.asarray(courant.shape, dtype=np.int64)
+    lib().oracle_calculate_displacement(
+        ctypes.c_int(dim), ctypes.c_int(n_dims), ctypes.c_int(int(implicit_in_space)),
+        _p(displacement), _p(courant), _p(shape), _p(cell_origin), _p(position_in_cell), i64(n_sd),
+        f64(n_substeps))
+
+
+def flag_precipitated(cell_origin, position_in_cell, water_mass, multiplicity, idx, length,
+                      healthy, precipitation_counting_level_index, displacement):
+    return float(lib().oracle_flag_precipitated(
+        _p(np.ascontiguousarray(cell_origin[-1])), _p(np.ascontiguousarray(position_in_cell[-1])),
+        _p(water_mass), _p(multiplicity), _p(idx), i64(length), i64(len(idx)), _p(healthy),
+        f64(precipitation_counting_level_index), _p(np.ascontiguousarray(displacement[-1]))))
+
+
+def flag_out_of_column(cell_origin, position_in_cell, idx, length, healthy,
+                       domain_top_level_index):
+    lib().oracle_flag_out_of_column(
+        _p(np.ascontiguousarray(cell_origin[-1])), _p(np.ascontiguousarray(position_in_cell[-1])),
+        _p(idx), i64(length), i64(len(idx)), _p(healthy), f64(domain_top_level_index))
+
+
+def update_position(cell_origin, position_in_cell, displacement, floor_of_position, grid,
+                    apply_boundary=True):
+    """Displacement.update_position + update_cell_origin (+ boundary_condition)"""
+    n_dims, n_sd = position_in_cell.shape
+    lib().oracle_update_position(_p(cell_origin), _p(position_in_cell), _p(displacement),
+                                 _p(floor_of_position), _p(grid), i64(n_dims), i64(n_sd),
+                                 ctypes.c_int(int(apply_boundary)))

@@ -67,6 +67,16 @@ SIGNATURES = {
         INT, (P,) * 14 + (I64, F64, INT, F64, P)),
     "pysdm_b200_ll82_fragmentation": (INT, (P,) * 14 + (I64, F64, F64, INT, F64, P)),
     "pysdm_b200_ll82_coalescence_check": (INT, (P, P, I64, P)),
+    "pysdm_b200_floor_to_i64": (INT, (P, P, I64, P)),
+    "pysdm_b200_sub_i64": (INT, (P, P, I64, P)),
+    "pysdm_b200_row_modulo_i64": (INT, (P, P, I64, I64, P)),
+    "pysdm_b200_moments": (
+        INT, (P, P, P, P, P, P, I64, P, I64, F64, F64, P, P, F64, INT, INT, I64, P)),
+    "pysdm_b200_spectrum_moments": (
+        INT, (P, P, P, P, P, P, I64, F64, INT, P, I64, P, P, F64, INT, I64, P)),
+    "pysdm_b200_calculate_displacement": (INT, (INT, INT, INT, P, P, P, P, P, I64, F64, P)),
+    "pysdm_b200_flag_precipitated": (INT, (P, P, P, P, P, I64, I64, P, F64, P, P, P)),
+    "pysdm_b200_flag_out_of_column": (INT, (P, P, P, I64, I64, P, F64, P)),
     "pysdm_b200_collision_coalescence_breakup": (
         INT, (P, P, I64, P, I64, I64) + (P,) * 11 + (F64, P, INT, P, P)),
 }

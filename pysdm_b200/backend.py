@@ -270,6 +270,48 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
             raise AttributeError(
                 f"Formulae(fragmentation_function='{name}') required (got '{have}')")
 
+    # ---- products side: moments_methods.py:12-182 -----------------------------------------------
+    @staticmethod
+    def moments(*, moment_0, moments, multiplicity, attr_data, cell_id, idx, length, ranks, min_x,
+                max_x, x_attr, weighting_attribute, weighting_rank, skip_division_by_m0):
+        m.moments(moment_0.data, moments.data, multiplicity.data, attr_data.data, cell_id.data,
+                  idx.data, length, ranks.to_ndarray(), min_x, max_x, x_attr.data,
+                  weighting_attribute.data, weighting_rank, skip_division_by_m0)
+
+    @staticmethod
+    def spectrum_moments(*, moment_0, moments, multiplicity, attr_data, cell_id, idx, length, rank,
+                         x_bins, x_attr, weighting_attribute, weighting_rank):
+        assert moments.shape[0] == x_bins.shape[0] - 1
+        assert moment_0.shape == moments.shape
+        m.spectrum_moments(moment_0.data, moments.data, multiplicity.data, attr_data.data,
+                           cell_id.data, idx.data, length, rank, x_bins.data, x_attr.data,
+                           weighting_attribute.data, weighting_rank)
+
+    # ---- transport side: displacement_methods.py:14-260 -----------------------------------------
+    def calculate_displacement(self, *, dim, displacement, courant, cell_origin, position_in_cell,
+                               n_substeps):
+        scheme = getattr(self.formulae.particle_advection, "__name__", "ImplicitInSpace")
+        if scheme not in ("ImplicitInSpace", "ExplicitInSpace"):
+            raise NotImplementedError(f"particle_advection={scheme}")
+        if len(courant.shape) > 3:
+            raise NotImplementedError()
+        m.calculate_displacement(dim, displacement.data, courant.data, cell_origin.data,
+                                 position_in_cell.data, n_substeps,
+                                 implicit_in_space=scheme == "ImplicitInSpace")
+
+    @staticmethod
+    def flag_precipitated(*, cell_origin, position_in_cell, water_mass, multiplicity, idx, length,
+                          healthy, precipitation_counting_level_index, displacement) -> float:
+        return m.flag_precipitated(cell_origin.data, position_in_cell.data, water_mass.data,
+                                   multiplicity.data, idx.data, length, healthy.data,
+                                   precipitation_counting_level_index, displacement.data)
+
+    @staticmethod
+    def flag_out_of_column(cell_origin, position_in_cell, idx, length, healthy,
+                           domain_top_level_index):
+        m.flag_out_of_column(cell_origin.data, position_in_cell.data, idx.data, length,
+                             healthy.data, domain_top_level_index)
+
     # ---- physics (physics_methods.py:107-133) -----------------------------------------------
     def volume_of_water_mass(self, volume, mass):
         m.volume_of_water_mass(volume.data, mass.data, self.rho_w)
@@ -280,8 +322,7 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
 
 # everything outside the collision path: explicit NotImplementedError
 for _name in (
-        "condensation", "make_condensation_solver", "calculate_displacement", "flag_precipitated",
-        "flag_out_of_column", "moments", "spectrum_moments", "seeding", "freeze_singular",
+        "condensation", "make_condensation_solver", "seeding", "freeze_singular",
         "freeze_time_dependent", "freeze_time_dependent_homogeneous", "thaw_instantaneous",
         "oxidation", "dissolution", "chem_recalculate_drop_data", "chem_recalculate_cell_data",
         "equilibrate_H", "isotopic_delta", "isotopic_fractionation", "deposition",

@@ -97,6 +97,53 @@ PYSDM_EXPORT int pysdm_b200_row_modulo(double *out, const double *divisor, i64 n
     return LAUNCH_CHECK();
 }
 
+// ---- mixed int64 / fp64 operators of Displacement (dynamics/displacement.py:141-153) ------
+__global__ void k_floor_to_i64(i64 *__restrict__ out, const double *__restrict__ in, i64 n)
+{
+    i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (i64)floor(in[i]);
+}
+
+__global__ void k_sub_i64(double *__restrict__ inout, const i64 *__restrict__ b, i64 n)
+{
+    i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) inout[i] -= (double)b[i];
+}
+
+__global__ void k_row_modulo_i64(i64 *__restrict__ out, const i64 *__restrict__ divisor,
+                                 i64 n_rows, i64 n_cols)
+{
+    i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rows * n_cols) return;
+    const i64 d = divisor[i / n_cols];
+    i64 r = out[i] % d;  // numpy's %: the result takes the sign of the divisor
+    if (r != 0 && ((r < 0) != (d < 0))) r += d;
+    out[i] = r;
+}
+
+PYSDM_EXPORT int pysdm_b200_floor_to_i64(i64 *out, const double *in, i64 n, void *stream)
+{
+    if (n <= 0) return 0;
+    k_floor_to_i64<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(out, in, n);
+    return LAUNCH_CHECK();
+}
+
+PYSDM_EXPORT int pysdm_b200_sub_i64(double *inout, const i64 *b, i64 n, void *stream)
+{
+    if (n <= 0) return 0;
+    k_sub_i64<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(inout, b, n);
+    return LAUNCH_CHECK();
+}
+
+PYSDM_EXPORT int pysdm_b200_row_modulo_i64(i64 *out, const i64 *divisor, i64 n_rows, i64 n_cols,
+                                           void *stream)
+{
+    if (n_rows * n_cols <= 0) return 0;
+    k_row_modulo_i64<<<grid_for(n_rows * n_cols), kThreads, 0, (cudaStream_t)stream>>>(
+        out, divisor, n_rows, n_cols);
+    return LAUNCH_CHECK();
+}
+
 // ---- reductions: amin / amax with numpy NaN propagation ---------------------------
 constexpr int kReduceBlocks = 592;  // 4 per SM on 148 SMs
 

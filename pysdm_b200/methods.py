@@ -379,3 +379,77 @@ def collision_coalescence_breakup(multiplicity, idx, length, attributes, gamma, 
         int(bool(handle_all_breakups)), _pi(counter), _stream()),
         "collision_coalescence_breakup")
     return int(counter.item()) if count_overflows else None
+
+
+# ---- products and transport side (csrc/transport.cu) ------------------------------
+def _is_int(x):
+    import numbers  # pylint: disable=import-outside-toplevel
+
+    return int(isinstance(x, numbers.Integral) and not isinstance(x, bool))
+
+
+def moments(moment_0, moments_, multiplicity, attr_data, cell_id_, idx, length, ranks, min_x,
+            max_x, x_attr, weighting_attribute, weighting_rank, skip_division_by_m0):
+    """`ranks`: host sequence of floats (the reference's `ranks` storage holds floats)"""
+    ranks = [float(r) for r in ranks]
+    check(_lib.load().pysdm_b200_moments(
+        _pf(moment_0), _pf(moments_), _pi(multiplicity), _pf(attr_data) if ranks else None,
+        _pi(cell_id_), _pi(idx), int(length), _host_f64(ranks) if ranks else None, len(ranks),
+        float(min_x), float(max_x), _pf(x_attr), _pf(weighting_attribute), float(weighting_rank),
+        _is_int(weighting_rank), int(bool(skip_division_by_m0)), moment_0.numel(), _stream()),
+        "moments")
+
+
+def spectrum_moments(moment_0, moments_, multiplicity, attr_data, cell_id_, idx, length, rank,
+                     x_bins, x_attr, weighting_attribute, weighting_rank):
+    n_bins, n_cell = moments_.shape
+    assert x_bins.numel() == n_bins + 1 and tuple(moment_0.shape) == (n_bins, n_cell)
+    check(_lib.load().pysdm_b200_spectrum_moments(
+        _pf(moment_0), _pf(moments_), _pi(multiplicity), _pf(attr_data), _pi(cell_id_), _pi(idx),
+        int(length), float(rank), _is_int(rank), _pf(x_bins), n_bins, _pf(x_attr),
+        _pf(weighting_attribute), float(weighting_rank), _is_int(weighting_rank), n_cell,
+        _stream()), "spectrum_moments")
+
+
+def calculate_displacement(dim, displacement, courant, cell_origin, position_in_cell, n_substeps,
+                           implicit_in_space=True):
+    n_dims, n_sd = displacement.shape
+    assert courant.dim() == n_dims
+    shape = (ctypes.c_int64 * n_dims)(*courant.shape)
+    check(_lib.load().pysdm_b200_calculate_displacement(
+        int(dim), n_dims, int(bool(implicit_in_space)), _pf(displacement), _pf(courant), shape,
+        _pi(cell_origin), _pf(position_in_cell), n_sd, float(n_substeps), _stream()),
+        "calculate_displacement")
+
+
+def flag_precipitated(cell_origin, position_in_cell, water_mass, multiplicity, idx, length,
+                      healthy, precipitation_counting_level_index, displacement):
+    """returns the rainfall mass (host float; synchronises)"""
+    rain = torch.zeros(1, dtype=torch.float64, device=idx.device)
+    check(_lib.load().pysdm_b200_flag_precipitated(
+        _pi(cell_origin[-1]), _pf(position_in_cell[-1]), _pf(water_mass), _pi(multiplicity),
+        _pi(idx), int(length), idx.numel(), _pi(healthy),
+        float(precipitation_counting_level_index), _pf(displacement[-1]), _pf(rain), _stream()),
+        "flag_precipitated")
+    return float(rain.item())
+
+
+def flag_out_of_column(cell_origin, position_in_cell, idx, length, healthy,
+                       domain_top_level_index):
+    check(_lib.load().pysdm_b200_flag_out_of_column(
+        _pi(cell_origin[-1]), _pf(position_in_cell[-1]), _pi(idx), int(length), idx.numel(),
+        _pi(healthy), float(domain_top_level_index), _stream()), "flag_out_of_column")
+
+
+def floor_to_int(out, src):
+    check(_lib.load().pysdm_b200_floor_to_i64(_pi(out), _pf(src), src.numel(), _stream()), "floor")
+
+
+def sub_int(inout, b):
+    check(_lib.load().pysdm_b200_sub_i64(_pf(inout), _pi(b), b.numel(), _stream()), "sub_int")
+
+
+def row_modulo_int(out, divisor):
+    n_rows, n_cols = out.shape if out.dim() == 2 else (1, out.numel())
+    check(_lib.load().pysdm_b200_row_modulo_i64(_pi(out), _pi(divisor), n_rows, n_cols,
+                                                _stream()), "row_modulo")

@@ -201,6 +201,11 @@ class Storage(StorageBase):
         return self._ew("add", self.data, tensor, scalar)
 
     def __isub__(self, other):
+        if self.dtype is Storage.FLOAT and getattr(other, "dtype", None) is Storage.INT:
+            # position_in_cell -= floor_of_position (dynamics/displacement.py:150)
+            _lib.check(_lib.load().pysdm_b200_sub_i64(ptr(self.data), ptr(other.data),
+                                                     self.data.numel(), stream()), "sub_int")
+            return self
         return self._ew("sub", self.data, other.data)
 
     def __imul__(self, other):
@@ -213,6 +218,10 @@ class Storage(StorageBase):
 
     def __imod__(self, other):
         n_rows, n_cols = (self.shape if len(self.shape) == 2 else (1, self.shape[0]))
+        if self.dtype is Storage.INT:  # cell_origin %= grid (dynamics/displacement.py:152-153)
+            _lib.check(_lib.load().pysdm_b200_row_modulo_i64(
+                ptr(self.data), ptr(other.data), n_rows, n_cols, stream()), "row_modulo")
+            return self
         _lib.check(_lib.load().pysdm_b200_row_modulo(ptr(self.data), ptr(other.data), n_rows,
                                                     n_cols, stream()), "row_modulo")
         return self
@@ -221,6 +230,10 @@ class Storage(StorageBase):
         return self._ew("pow", self.data, None, float(other))
 
     def floor(self, other=None):
+        if self.dtype is Storage.INT:  # floor_of_position.floor(position_in_cell), :147-148
+            _lib.check(_lib.load().pysdm_b200_floor_to_i64(
+                ptr(self.data), ptr(other.data), self.data.numel(), stream()), "floor")
+            return self
         return self._ew("floor", None, self.data if other is None else other.data)
 
     def product(self, multiplicand, multiplier):

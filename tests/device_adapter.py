@@ -258,3 +258,68 @@ def collision_coalescence_breakup(multiplicity, idx, length, attributes, gamma, 
                                           count_overflows=True)
     m.back(0, 2, 8, 10, 11, 12)
     return n
+
+
+# ---- products and transport side ---------------------------------------------------------------
+def moments(moment_0, moments_, multiplicity, attr_data, cell_id_, idx, length, ranks, min_x,
+            max_x, x_attr, weighting_attribute, weighting_rank, skip_division_by_m0):
+    m = _Mirror(moment_0, moments_, multiplicity, attr_data, cell_id_, idx, x_attr,
+                weighting_attribute)
+    d = m.dev
+    dev.moments(d[0], d[1], d[2], d[3], d[4], d[5], length, ranks, min_x, max_x, d[6], d[7],
+                weighting_rank, skip_division_by_m0)
+    m.back(0, 1)
+
+
+def spectrum_moments(moment_0, moments_, multiplicity, attr_data, cell_id_, idx, length, rank,
+                     x_bins, x_attr, weighting_attribute, weighting_rank):
+    m = _Mirror(moment_0, moments_, multiplicity, attr_data, cell_id_, idx, x_bins, x_attr,
+                weighting_attribute)
+    d = m.dev
+    dev.spectrum_moments(d[0], d[1], d[2], d[3], d[4], d[5], length, rank, d[6], d[7], d[8],
+                         weighting_rank)
+    m.back(0, 1)
+
+
+def calculate_displacement(dim, displacement, courant, cell_origin, position_in_cell, n_substeps,
+                           implicit_in_space=True):
+    m = _Mirror(displacement, courant, cell_origin, position_in_cell)
+    dev.calculate_displacement(dim, *m.dev, n_substeps, implicit_in_space=implicit_in_space)
+    m.back(0)
+
+
+def flag_precipitated(cell_origin, position_in_cell, water_mass, multiplicity, idx, length,
+                      healthy, precipitation_counting_level_index, displacement):
+    m = _Mirror(cell_origin, position_in_cell, water_mass, multiplicity, idx, healthy,
+                displacement)
+    d = m.dev
+    rain = dev.flag_precipitated(d[0], d[1], d[2], d[3], d[4], length, d[5],
+                                 precipitation_counting_level_index, d[6])
+    m.back(4, 5)
+    return rain
+
+
+def flag_out_of_column(cell_origin, position_in_cell, idx, length, healthy,
+                       domain_top_level_index):
+    m = _Mirror(cell_origin, position_in_cell, idx, healthy)
+    dev.flag_out_of_column(*m.dev[:3], length, m.dev[3], domain_top_level_index)
+    m.back(2, 3)
+
+
+def update_position(cell_origin, position_in_cell, displacement, floor_of_position, grid,
+                    apply_boundary=True):
+    """the Storage operator sequence of Displacement (dynamics/displacement.py:138-153)
+    through pysdm_b200.storage.Storage"""
+    from pysdm_b200.storage import Storage  # pylint: disable=import-outside-toplevel
+
+    s_origin, s_pos = Storage.from_ndarray(cell_origin), Storage.from_ndarray(position_in_cell)
+    s_disp, s_tmp = Storage.from_ndarray(displacement), Storage.from_ndarray(floor_of_position)
+    s_pos += s_disp
+    s_tmp.floor(s_pos)
+    s_origin += s_tmp
+    s_pos -= s_tmp
+    if apply_boundary:
+        s_origin %= Storage.from_ndarray(grid)
+    cell_origin[...] = s_origin.to_ndarray()
+    position_in_cell[...] = s_pos.to_ndarray()
+    floor_of_position[...] = s_tmp.to_ndarray()

@@ -351,6 +351,30 @@ int pysdm_b200_flag_out_of_column(const int64_t *cell_origin_z, const double *po
                                   int64_t *idx, int64_t length, int64_t idx_len,
                                   int64_t *healthy, double domain_top_level_index, void *stream);
 
+/* ---- migration between the slabs of a multi-GPU run (no reference counterpart: PySDM is
+ * single-process; data model of PySDM/impl/particle_attributes.py) ---------------------------
+ * The first grid dimension is split into `world` balanced contiguous slabs.  A record is
+ * R = 1 + n_attr + 2 n_dims int64 words: multiplicity, attributes (fp64 bits), cell origin
+ * (global coordinates), position in cell (fp64 bits). */
+
+/* for every working position: dest[i] = owner rank of SD i = idx[p], cell_id[i] = cell id local
+ * to the owner's slab; host_grid = grid size per dimension (HOST array) */
+int pysdm_b200_migration_destination(int64_t *dest, int64_t *cell_id, const int64_t *cell_origin,
+                                     const int64_t *idx, int64_t length, int64_t n_sd, int n_dims,
+                                     const int64_t *host_grid, int64_t world, void *stream);
+/* records[r, :] <- SD order[q], q = r skipping [own_begin, own_begin + own_count) (`order` =
+ * idx sorted by destination rank); the multiplicity of a packed SD is zeroed (slot vacant) */
+int pysdm_b200_migration_pack(int64_t *records, int64_t n_rows, const int64_t *order,
+                              int64_t own_begin, int64_t own_count, int64_t *multiplicity,
+                              const double *attributes, int64_t n_attr,
+                              const int64_t *cell_origin, const double *position_in_cell,
+                              int n_dims, int64_t n_sd, void *stream);
+/* SD slots[r] <- records[r, :]; idx_tail[r] = slots[r] (idx_tail = idx + working length) */
+int pysdm_b200_migration_unpack(const int64_t *records, int64_t n_rows, const int64_t *slots,
+                                int64_t *idx_tail, int64_t *multiplicity, double *attributes,
+                                int64_t n_attr, int64_t *cell_origin, double *position_in_cell,
+                                int n_dims, int64_t n_sd, void *stream);
+
 /* PYSDM_B200_H_END_OF_METHOD_LEVEL -- fused step and later additions follow */
 
 #ifdef __cplusplus

@@ -117,3 +117,40 @@ def test_sharded_steps_equal_global_step():
         np.testing.assert_array_equal(part.multiplicity, whole.multiplicity[gi])
         np.testing.assert_array_equal(part.attributes[0], whole.attributes[0][gi])
     assert whole.coalescence_rate.sum() > 0
+
+
+def _exchange_worker(rank, world, port, out_dir):
+    """pysdm_b200.migration.exchange (the all-to-all-v of migrating super-droplet records) on
+    CPU tensors over gloo: rank r sends r + d + 1 rows to rank d (none to itself), every word
+    tagged with (source, destination, row)"""
+    from pysdm_b200.migration import exchange  # pylint: disable=import-outside-toplevel
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        n_words = 5
+
+        def rows(src, dst):
+            n = 0 if src == dst else src + dst + 1
+            base = (src * 100 + dst * 10) * 1000
+            return (base + torch.arange(n, dtype=torch.int64)[:, None] * n_words
+                    + torch.arange(n_words, dtype=torch.int64)[None, :])
+
+        send = torch.cat([rows(rank, d) for d in range(world)])
+        counts = [0 if d == rank else rank + d + 1 for d in range(world)]
+        recv, recv_counts = exchange(send, counts)
+        assert recv_counts == [0 if s == rank else s + rank + 1 for s in range(world)]
+        assert torch.equal(recv, torch.cat([rows(s, rank) for s in range(world)]))
+        # a rank with nothing to send or receive still takes part
+        recv, recv_counts = exchange(torch.empty((0, n_words), dtype=torch.int64), [0] * world)
+        assert recv.shape == (0, n_words) and recv_counts == [0] * world
+        with open(os.path.join(out_dir, f"ok{rank}"), "w", encoding="utf-8") as f:
+            f.write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_migration_exchange_gloo_world2(tmp_path):
+    world = 2
+    mp.spawn(_exchange_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(world))

@@ -1,0 +1,115 @@
+"""Supplementary timings (NOT the bench.py contract): BASELINE.json configs[0..2] -- the
+single-cell boxes -- at their stated sizes, run through the UNMODIFIED PySDM orchestration
+(baseline/_ref) once with `pysdm_b200.B200` and once with the reference's Numba CPU backend.
+These configurations use the method-level kernels (one giant cell does not fit the fused
+step): what is measured is the drop-in backend as a PySDM user sees it, Python orchestration
+included.
+
+    python profiles/tools/bench_configs.py [--steps 10] [--cpu-steps 2] [--configs 0,1,2]
+
+One JSON line per (config, backend)."""
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle", "refshims"))
+_REF = next((p for p in (os.path.join(ROOT, "baseline", "_ref"), "/root/reference")
+             if os.path.isdir(os.path.join(p, "PySDM"))), None)
+sys.path.insert(1, _REF)
+os.environ.setdefault("CI", "1")
+np.NaN = np.nan
+
+
+def dynamics(config):
+    from PySDM.dynamics import Coalescence, Collision
+    from PySDM.dynamics.collisions.breakup_efficiencies import ConstEb
+    from PySDM.dynamics.collisions.breakup_fragmentations import Straub2010Nf
+    from PySDM.dynamics.collisions.coalescence_efficiencies import Straub2010Ec
+    from PySDM.dynamics.collisions.collision_kernels import Geometric, Golovin, Hydrodynamic
+    from PySDM.physics import si
+
+    if config == 0:  # Shima et al. 2009 box
+        return Coalescence(collision_kernel=Golovin(b=1.5e3), adaptive=False)
+    if config == 1:  # Berry 1967 box
+        return Coalescence(collision_kernel=Hydrodynamic(), adaptive=True,
+                           dt_coal_range=(0.1, 100.0))
+    vmin = (0.01 * si.mm) ** 3 * np.pi / 6  # de Jong et al. breakup box
+    return Collision(collision_kernel=Geometric(), coalescence_efficiency=Straub2010Ec(),
+                     breakup_efficiency=ConstEb(1.0),
+                     fragmentation_function=Straub2010Nf(vmin=vmin, nfmax=10000), adaptive=True,
+                     warn_overflows=False)
+
+
+SETUP = {
+    0: dict(name="Shima 2009 box, Golovin, 2^17 SDs", log2=17, dt=1.0, dv=1e6, r0=30.531e-6,
+            norm=2 ** 23 * 1e6, fkw={}),
+    1: dict(name="Berry 1967 box, Hydrodynamic + adaptive, 2^20 SDs", log2=20, dt=10.0, dv=10.0,
+            r0=10e-6, norm=239e6 * 10, fkw={}),
+    2: dict(name="de Jong 2022 breakup box, Geometric + Straub, 2^22 SDs", log2=22, dt=1.0,
+            dv=1e6, r0=0.2e-3, norm=1e3 * 1e6,
+            fkw={"fragmentation_function": "Straub2010Nf"}),
+}
+
+
+def run(config, backend_name, steps, log2=None):
+    from PySDM import Builder, Formulae
+    from PySDM.environments import Box
+
+    c = SETUP[config]
+    n_sd = 1 << (log2 or c["log2"])
+    rng = np.random.default_rng(44)
+    x0 = 4 / 3 * np.pi * c["r0"] ** 3
+    volume = rng.exponential(x0, n_sd)
+    attributes = {"volume": volume,
+                  "multiplicity": np.full(n_sd, max(1, int(c["norm"] / n_sd)), dtype=np.int64)}
+    formulae = Formulae(seed=44, **c["fkw"])
+    if backend_name == "B200":
+        from pysdm_b200 import B200
+
+        backend = B200(formulae)
+    else:
+        from PySDM.backends import CPU
+
+        backend = CPU(formulae)
+    builder = Builder(n_sd=n_sd, backend=backend, environment=Box(dv=c["dv"], dt=c["dt"]))
+    builder.add_dynamic(dynamics(config))
+    particulator = builder.build(attributes=attributes, products=())
+    particulator.run(2)  # warm-up (JIT / workspaces)
+    sync = (lambda: None)
+    if backend_name == "B200":
+        import torch
+
+        sync = torch.cuda.synchronize
+    sync()
+    t0 = time.perf_counter()
+    particulator.run(steps)
+    sync()
+    dt = time.perf_counter() - t0
+    dyn = particulator.dynamics["Collision"]
+    substeps = float(np.mean(dyn.stats_n_substep.to_ndarray())) if config else float(steps + 2)
+    print(json.dumps({
+        "config": c["name"], "backend": backend_name, "n_sd": n_sd, "steps": steps,
+        "ms_per_step": dt / steps * 1e3, "sd_steps_per_s": n_sd * steps / dt,
+        "substeps_since_start": substeps,
+        "threads": os.environ.get("NUMBA_NUM_THREADS", "default") if backend_name == "CPU" else None,
+        "super_droplets_left": int(particulator.attributes.super_droplet_count)}), flush=True)
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--cpu-steps", type=int, default=2)
+    ap.add_argument("--configs", default="0,1,2")
+    ap.add_argument("--backends", default="B200,CPU")
+    ap.add_argument("--log2", type=int, default=None)
+    a = ap.parse_args()
+    for cfg in (int(x) for x in a.configs.split(",")):
+        for be in a.backends.split(","):
+            run(cfg, be, a.steps if be == "B200" else a.cpu_steps, a.log2)

@@ -206,6 +206,7 @@ typedef struct pysdm_b200_fused_args {
                                    clears healthy[0] stores its `epoch` in gate[0].  The caller
                                    zeroes gate[0] when it has removed the zero-multiplicity SDs. */
     int64_t epoch;              /* != 0, different for consecutive launches */
+    uint32_t philox_round_keys[20]; /* filled in by the launcher from `seed` */
 } pysdm_b200_fused_args;
 
 int64_t pysdm_b200_fused_max_cell_size(void);

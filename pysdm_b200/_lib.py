@@ -97,7 +97,8 @@ class FusedArgs(ctypes.Structure):
         + [(n, U64) for n in ("seed", "call_u01", "call_rand")]
         + [(n, F64) for n in ("timestep", "dv", "rho_w", "substeps", "kernel_a", "kernel_b")]
         + [("kernel", ctypes.c_int32), ("reserved", ctypes.c_int32), ("max_cell_size", I64),
-           ("nf_slot", P), ("refresh_nf", I64), ("gate", P), ("epoch", I64)])
+           ("nf_slot", P), ("refresh_nf", I64), ("gate", P), ("epoch", I64),
+           ("philox_round_keys", U32 * 20)])
 
 
 KERNELS = {"Golovin": 0, "ConstantK": 1, "Linear": 2}

@@ -53,6 +53,7 @@ enum { KERNEL_GOLOVIN = 0, KERNEL_CONSTANT_K = 1, KERNEL_LINEAR = 2 };
 constexpr int kFusedThreads = 256;
 constexpr int kCtaPos = 8192, kCtaCells = 256;  // CTA group: positions / cells per batch
 constexpr int kWarpPos = PYSDM_WARP_POS, kWarpCells = 32;  // warp group
+static_assert(kWarpCells <= 32, "cell number and pair role share one byte (5 + 2 bits)");
 constexpr double kTwo52 = 4503599627370496.0;    // 2^52
 
 // ---- exact arithmetic helpers without XU-pipe instructions ---------------------------------
@@ -178,8 +179,8 @@ __device__ __forceinline__ void counter_add(i64 *counters, i64 cid, i64 value, b
 // multiplicity (cheap, cached) instead of being carried through the queue.
 template <int K, bool kAggregate>
 __device__ __forceinline__ void process_hits(const FusedArgs &a, u32 pf, double g_raw, bool mine,
-                                             const u32 *sd, const u8 *cellof, const i64 *cidv,
-                                             double *gamma_b)
+                                             const u32 *sd, const u8 *cellof, u32 cell_mask,
+                                             const i64 *cidv, double *gamma_b)
 {
     bool active = false;
     i64 cid = 0, add_rate = 0, add_deficit = 0, add_coal = 0;
@@ -199,7 +200,7 @@ __device__ __forceinline__ void process_hits(const FusedArgs &a, u32 pf, double 
         }
         const double gamma = i64_to_f64(g);
         if (g != gi) gamma_b[pf >> 1] = gamma;
-        cid = cidv[cellof[pf]];
+        cid = cidv[cellof[pf] & cell_mask];
         add_rate = g * n_k;
         add_deficit = (gi - g) * n_k;
         active = true;
@@ -241,6 +242,8 @@ template <int K, bool kPhilox, bool kWarp, bool kAggregate>
 __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(const FusedArgs a)
 {
     typedef Geo<kWarp> G;
+    constexpr u32 kCellMask = kWarp ? 0x1fu : 0xffu;  // cellof[] entry -> cell number
+    constexpr u32 kRoleFirst = 0x20u, kRoleSingle = 0x40u;
     extern __shared__ __align__(16) unsigned char smem_all[];
     const int tid = threadIdx.x;
     const int group = kWarp ? (tid >> 5) : 0;
@@ -299,7 +302,13 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     if (kWarp) {
         for (int c = 0; c < ncb; ++c) {
             const int s = cs[c], e = cs[c + 1];
-            for (int lp = s + gt; lp < e; lp += 32) cellof[lp] = (u8)c;
+            // warp groups (<= 32 cells per batch): bits 0-4 = cell, bit 5 = first of a pair,
+            // bit 6 = unpaired last SD of an odd cell (find_pairs, pair_methods.py:38-41)
+            for (int lp = s + gt; lp < e; lp += 32) {
+                const bool even = ((lp - s) & 1) == 0, partner = lp + 1 < e;
+                cellof[lp] = (u8)(c | (even && partner ? kRoleFirst : 0) |
+                                  (even && !partner ? kRoleSingle : 0));
+            }
         }
     } else {
         for (int c = tid >> 5; c < ncb; c += kFusedThreads / 32) {
@@ -343,7 +352,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
             for (int q = 0; q < 2; ++q) {
                 const int lp = lp0 + q;
                 if (lp < lo || lp >= P) continue;
-                const int c = cellof[lp];
+                const int c = cellof[lp] & kCellMask;
                 const int s = cs[c], len = cs[c + 1] - s;
                 // index_methods.py:40: j = int(cell_start[c] + u01[i] * (cell_end - cell_start));
                 // 0 <= x < 2^33: floor by a round-down add, integer in the low mantissa bits
@@ -372,8 +381,8 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
         auto philox_pair = [&](int lp0, double &u0, double &u1) {
             u32 w[4];
             const u64 b = blk_b + (u32)(lp0 >> 1);  // block = elements 2b, 2b + 1
-            philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_u01, (u32)(a.call_u01 >> 32),
-                          (u32)a.seed, (u32)(a.seed >> 32), w);
+            philox4x32_10_rk((u32)b, (u32)(b >> 32), (u32)a.call_u01, (u32)(a.call_u01 >> 32),
+                             a.philox_round_keys, w);
             u0 = u01_from_words(w[0], w[1]);
             u1 = u01_from_words(w[2], w[3]);
         };
@@ -472,17 +481,28 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
             const bool v0 = lp0 >= lo && lp0 < P, v1 = lp1 >= lo && lp1 < P;
             bool first0 = false, first1 = false, single0 = false, single1 = false;
             int c0l = 0, c1l = 0;
-            if (v0) {
-                c0l = cellof[lp0];
-                const bool even = ((lp0 - cs[c0l]) & 1) == 0, partner = lp0 + 1 < cs[c0l + 1];
-                first0 = even && partner;
-                single0 = even && !partner;
-            }
-            if (v1) {
-                c1l = cellof[lp1];
-                const bool even = ((lp1 - cs[c1l]) & 1) == 0, partner = lp1 + 1 < cs[c1l + 1];
-                first1 = even && partner;
-                single1 = even && !partner;
+            if (kWarp) {  // roles were packed next to the cell number in phase 1
+                const u32 both = *reinterpret_cast<const u16 *>(cellof + lp0);  // lp0 is even
+                const u32 b0 = v0 ? (both & 0xffu) : 0u, b1 = v1 ? (both >> 8) : 0u;
+                c0l = (int)(b0 & kCellMask);
+                c1l = (int)(b1 & kCellMask);
+                first0 = (b0 & kRoleFirst) != 0;
+                single0 = (b0 & kRoleSingle) != 0;
+                first1 = (b1 & kRoleFirst) != 0;
+                single1 = (b1 & kRoleSingle) != 0;
+            } else {
+                if (v0) {
+                    c0l = cellof[lp0];
+                    const bool even = ((lp0 - cs[c0l]) & 1) == 0, partner = lp0 + 1 < cs[c0l + 1];
+                    first0 = even && partner;
+                    single0 = even && !partner;
+                }
+                if (v1) {
+                    c1l = cellof[lp1];
+                    const bool even = ((lp1 - cs[c1l]) & 1) == 0, partner = lp1 + 1 < cs[c1l + 1];
+                    first1 = even && partner;
+                    single1 = even && !partner;
+                }
             }
             if (v0 && v1 && flag_al) {
                 *reinterpret_cast<u16 *>(flag_b + (u32)lp0) =
@@ -546,8 +566,8 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
             const int dl_mine = 2 * G::kSize * it + G::kSize * (lane >> 4) + wig + 2 * (lane & 15);
             u32 w[4];
             const u64 b = ((u64)base_al >> 2) + (u32)(dl_mine >> 1);
-            philox4x32_10((u32)b, (u32)(b >> 32), (u32)a.call_rand, (u32)(a.call_rand >> 32),
-                          (u32)a.seed, (u32)(a.seed >> 32), w);
+            philox4x32_10_rk((u32)b, (u32)(b >> 32), (u32)a.call_rand, (u32)(a.call_rand >> 32),
+                             a.philox_round_keys, w);
             const double r0 = u01_from_words(w[0], w[1]), r1 = u01_from_words(w[2], w[3]);
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
@@ -608,7 +628,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
             if (qn >= 32) {
                 qn -= 32;
                 process_hits<K, kAggregate>(a, q_pf[qn + (tid & 31)], q_g[qn + (tid & 31)], true, sd,
-                                            cellof, cidv, gamma_b);
+                                            cellof, kCellMask, cidv, gamma_b);
                 __syncwarp();
             }
         }
@@ -616,7 +636,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     if (qn > 0) {
         const bool mine = (tid & 31) < qn;
         process_hits<K, kAggregate>(a, mine ? q_pf[tid & 31] : 0u, mine ? q_g[tid & 31] : 0.0, mine, sd,
-                                    cellof, cidv, gamma_b);
+                                    cellof, kCellMask, cidv, gamma_b);
     }
 }
 
@@ -691,6 +711,10 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
     if (cpb > cap) cpb = cap;
     a.cells_per_batch = cpb;
     a.reserved = divisor_ok(a.rho_w) ? 1 : 0;
+    for (int r = 0; r < 10; ++r) {  // Philox4x32 key schedule (philox.cuh)
+        a.philox_round_keys[2 * r] = (u32)a.seed + (u32)r * 0x9E3779B9u;
+        a.philox_round_keys[2 * r + 1] = (u32)(a.seed >> 32) + (u32)r * 0xBB67AE85u;
+    }
     const i64 n_batches = (a.n_cell + cpb - 1) / cpb;
     const bool philox = a.u01 == nullptr;
     const bool aggregate = a.n_cell < 64;  // few counters: aggregate within the warp first

@@ -203,6 +203,52 @@ def test_host_step_stripes_equal_separate_runs():
     assert rate.sum() > 0 and host.h2d_bytes == mult.size * 8 * 4
 
 
+def test_full_size_properties_and_fused_equals_methods():
+    """BASELINE.json's headline size (2^24 super-droplets, 2^17 cells of 128, the bench.py
+    workload), where the oracle would take minutes: the fused step must equal the method-level
+    kernels bit for bit (same Philox stream), and the size-independent invariants of a
+    coalescence step must hold: idx stays a permutation, every cell keeps its droplets, the
+    number of pairs is sum(n_c // 2), the drop in total multiplicity equals the coalescence
+    counters exactly, and total water mass sum(n * m) is conserved to 1e-12"""
+    import torch  # pylint: disable=import-outside-toplevel
+
+    n_sd, per_cell = 1 << 24, 128
+    rng = np.random.default_rng(1234)
+    pop = {"multiplicity": rng.integers(1, 5, n_sd).astype(np.int64),
+           "water_mass": rng.exponential(1000 * 4 / 3 * np.pi * 30.531e-6 ** 3, n_sd),
+           "cell_id": np.arange(n_sd, dtype=np.int64) // per_cell, "n_cell": n_sd // per_cell}
+    sims = [device_sim(kernel=device_kernel(b=GOLOVIN_B), dt=1.0, dv=2e-7, seed=5, fused=f, **pop)
+            for f in (True, False)]
+    n0 = int(pop["multiplicity"].sum())
+    mass0 = float((pop["multiplicity"] * pop["water_mass"]).sum())
+    for step in range(2):
+        for s in sims:
+            s()
+        a, b = sims
+        assert a.length == b.length
+        for name in ("idx", "flag", "multiplicity", "attributes", "gamma", "coalescence_rate",
+                     "collision_rate", "collision_rate_deficit", "cell_start"):
+            x, y = getattr(a, name), getattr(b, name)
+            if name in ("idx", "flag"):
+                x, y = x[:a.length], y[:b.length]
+            if x.dtype == torch.float64:  # bit patterns (sign of zero, NaN fill beyond the length)
+                x, y = x.view(torch.int64), y.view(torch.int64)
+            assert torch.equal(x, y), f"step {step}: {name}"
+        idx = a.idx[:a.length]
+        assert int(torch.unique(idx).numel()) == a.length, "idx is not a permutation"
+        if a.sorted:  # (the removal of zero-multiplicity SDs leaves idx unsorted until the next step)
+            cells = a.cell_id[idx]
+            assert bool((cells[1:] >= cells[:-1]).all()), "idx no longer sorted by cell"
+        sizes = a.cell_start[1:] - a.cell_start[:-1]  # of the sort this step ran on
+        assert int(sizes.sum()) == a.sorted_length
+        assert int(a.flag[:a.sorted_length].sum()) == int((sizes // 2).sum())
+        n_now = int(a.multiplicity[idx].sum())
+        assert n0 - n_now == int(a.coalescence_rate.sum()) > 0
+        mass = float((a.multiplicity[idx].double() * a.attributes[0][idx]).sum())
+        assert abs(mass - mass0) <= 1e-12 * mass0
+    assert sims[0].n_fused_steps == 2 and sims[1].n_fused_steps == 0
+
+
 class _Host:  # pylint: disable=too-few-public-methods
     """numpy face of a DeviceCollision, shaped like OracleCollision for compare_states"""
 

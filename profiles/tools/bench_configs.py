@@ -40,6 +40,9 @@ def dynamics(config):
     if config == 1:  # Berry 1967 box
         return Coalescence(collision_kernel=Hydrodynamic(), adaptive=True,
                            dt_coal_range=(0.1, 100.0))
+    if config == 3:  # the collision step of the Sc-rain case (Morrison_and_Grabowski_2007/common.py:30-35)
+        return Coalescence(collision_kernel=Geometric(collection_efficiency=1), adaptive=True,
+                           optimized_random=True)
     vmin = (0.01 * si.mm) ** 3 * np.pi / 6  # de Jong et al. breakup box
     return Collision(collision_kernel=Geometric(), coalescence_efficiency=Straub2010Ec(),
                      breakup_efficiency=ConstEb(1.0),
@@ -55,6 +58,9 @@ SETUP = {
     2: dict(name="de Jong 2022 breakup box, Geometric + Straub, 2^22 SDs", log2=22, dt=1.0,
             dv=1e6, r0=0.2e-3, norm=1e3 * 1e6,
             fkw={"fragmentation_function": "Straub2010Nf"}),
+    # per-GPU share of configs[3]: 32768 cells of 128 SDs, dv of one cell of the 1.5 km / 512 grid
+    3: dict(name="Sc-rain collision step, Geometric + adaptive, 2^22 SDs in 32768 cells", log2=22,
+            dt=5.0, dv=(1500 / 512) ** 2, r0=10e-6, norm=None, fkw={}, sd_per_cell=128),
 }
 
 
@@ -67,8 +73,20 @@ def run(config, backend_name, steps, log2=None):
     rng = np.random.default_rng(44)
     x0 = 4 / 3 * np.pi * c["r0"] ** 3
     volume = rng.exponential(x0, n_sd)
-    attributes = {"volume": volume,
-                  "multiplicity": np.full(n_sd, max(1, int(c["norm"] / n_sd)), dtype=np.int64)}
+    env = Box(dv=c["dv"], dt=c["dt"])
+    if "sd_per_cell" in c:  # multi-cell: mesh set as tests/unit_tests/dynamics/collisions/test_sdm_multi_cell.py:25-27
+        from PySDM.impl.mesh import Mesh
+
+        n_cell = n_sd // c["sd_per_cell"]
+        env.mesh = Mesh((n_cell,), size=(n_cell,), dv=c["dv"])
+        # ~100 droplets / cm^3 in every cell, lognormal-ish radii around r0
+        volume = 4 / 3 * np.pi * (c["r0"] * np.exp(0.47 * rng.standard_normal(n_sd))) ** 3
+        attributes = {"volume": volume, "cell id": np.arange(n_sd, dtype=np.int64) // c["sd_per_cell"],
+                      "multiplicity": np.full(n_sd, int(100e6 * c["dv"] / c["sd_per_cell"]),
+                                              dtype=np.int64)}
+    else:
+        attributes = {"volume": volume, "multiplicity": np.full(
+            n_sd, max(1, int(c["norm"] / n_sd)), dtype=np.int64)}
     formulae = Formulae(seed=44, **c["fkw"])
     if backend_name == "B200":
         from pysdm_b200 import B200
@@ -78,7 +96,7 @@ def run(config, backend_name, steps, log2=None):
         from PySDM.backends import CPU
 
         backend = CPU(formulae)
-    builder = Builder(n_sd=n_sd, backend=backend, environment=Box(dv=c["dv"], dt=c["dt"]))
+    builder = Builder(n_sd=n_sd, backend=backend, environment=env)
     builder.add_dynamic(dynamics(config))
     particulator = builder.build(attributes=attributes, products=())
     particulator.run(2)  # warm-up (JIT / workspaces)

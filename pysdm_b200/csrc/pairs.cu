@@ -291,10 +291,12 @@ PYSDM_EXPORT int pysdm_b200_scale_prob_for_adaptive_sdm_gamma(
 __global__ void k_adaptive_end(const double *__restrict__ dt_left, i64 n_cell,
                                const i64 *__restrict__ cell_start, i64 *__restrict__ result)
 {
-    // single block; max over i with dt_left[i] != 0
+    // result (zeroed by the launcher) = max over cells i with dt_left[i] != 0 of cell_start[i+1]
+    // = cell_start[last such i + 1], because cell_start never decreases
     __shared__ i64 best[kThreads / 32];
     i64 m = -1;
-    for (i64 i = threadIdx.x; i < n_cell; i += blockDim.x)
+    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n_cell;
+         i += (i64)gridDim.x * blockDim.x)
         if (dt_left[i] != 0) m = i;  // i increases: the last hit is the largest for this thread
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -305,7 +307,7 @@ __global__ void k_adaptive_end(const double *__restrict__ dt_left, i64 n_cell,
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int w = 1; w < kThreads / 32; ++w) m = best[w] > m ? best[w] : m;
-        *result = m < 0 ? 0 : cell_start[m + 1];
+        if (m >= 0) atomicMax((long long *)result, (long long)cell_start[m + 1]);
     }
 }
 
@@ -314,8 +316,12 @@ PYSDM_EXPORT int pysdm_b200_adaptive_sdm_end(const double *dt_left, i64 n_cell,
                                              i64 *dev_scratch, void *stream)
 {
     cudaStream_t st = (cudaStream_t)stream;
-    k_adaptive_end<<<1, kThreads, 0, st>>>(dt_left, n_cell, cell_start, dev_scratch);
-    int err = LAUNCH_CHECK();
+    int err = (int)cudaMemsetAsync(dev_scratch, 0, sizeof(i64), st);
+    if (err) return err;
+    int blocks = grid_for(n_cell);
+    if (blocks > 148) blocks = 148;
+    k_adaptive_end<<<blocks, kThreads, 0, st>>>(dt_left, n_cell, cell_start, dev_scratch);
+    err = LAUNCH_CHECK();
     if (err) return err;
     err = (int)cudaMemcpyAsync(host_result, dev_scratch, sizeof(i64), cudaMemcpyDeviceToHost, st);
     if (err) return err;

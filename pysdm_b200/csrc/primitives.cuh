@@ -126,19 +126,23 @@ static inline void device_exclusive_scan(const T *in, T *out, i64 n, int with_to
 
 // ---------------------------------------------------------------------------------
 // stable LSD radix sort of (key, value) pairs, 8-bit digits.
-// One warp owns a contiguous chunk of kRadixChunk elements: per-(digit, chunk)
+// One warp owns a contiguous chunk of radix_chunk(n) elements: per-(digit, chunk)
 // histogram -> device scan (digit-major) -> each warp replays its chunk in order and
 // scatters with warp-private running offsets (stable by construction, no inter-warp
 // coordination, no atomics on global memory).
 // ---------------------------------------------------------------------------------
-constexpr int kRadixChunk = 1024;
 constexpr int kRadixWarps = kThreads / 32;
 constexpr int kRadixBins = 256;
+constexpr int kRadixGroup = 8;  // elements per lane loaded before any is consumed
+
+// elements per warp: small arrays (per-cell keys of sort_by_key, a few 10^4 elements) are cut
+// finer so that more than a handful of warps work on them
+static inline int radix_chunk(i64 n) { return n <= ((i64)1 << 18) ? 256 : 1024; }
 
 template <typename K>
 __global__ void __launch_bounds__(kThreads) radix_histogram(const K *__restrict__ keys, i64 n,
                                                             int shift, u32 *__restrict__ hist,
-                                                            i64 n_chunks)
+                                                            i64 n_chunks, int chunk_size)
 {
     __shared__ u32 cnt[kRadixWarps][kRadixBins];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -146,11 +150,19 @@ __global__ void __launch_bounds__(kThreads) radix_histogram(const K *__restrict_
     for (int d = lane; d < kRadixBins; d += 32) cnt[warp][d] = 0;
     __syncwarp();
     if (chunk < n_chunks) {
-        const i64 base = chunk * kRadixChunk;
-#pragma unroll 4
-        for (int g = 0; g < kRadixChunk / 32; ++g) {
-            i64 i = base + g * 32 + lane;
-            if (i < n) atomicAdd(&cnt[warp][(u32)(keys[i] >> shift) & 0xffu], 1u);
+        const i64 base = chunk * chunk_size;
+        for (int g0 = 0; g0 < chunk_size / 32; g0 += kRadixGroup) {
+            K key[kRadixGroup];
+#pragma unroll
+            for (int u = 0; u < kRadixGroup; ++u) {
+                const i64 i = base + (g0 + u) * 32 + lane;
+                key[u] = i < n ? keys[i] : K(0);
+            }
+#pragma unroll
+            for (int u = 0; u < kRadixGroup; ++u) {
+                const i64 i = base + (g0 + u) * 32 + lane;
+                if (i < n) atomicAdd(&cnt[warp][(u32)(key[u] >> shift) & 0xffu], 1u);
+            }
         }
         __syncwarp();
         for (int d = lane; d < kRadixBins; d += 32) hist[(i64)d * n_chunks + chunk] = cnt[warp][d];
@@ -161,7 +173,8 @@ template <typename K, typename V>
 __global__ void __launch_bounds__(kThreads)
     radix_scatter(const K *__restrict__ keys_in, const V *__restrict__ vals_in,
                   K *__restrict__ keys_out, V *__restrict__ vals_out, i64 n, int shift,
-                  const u32 *__restrict__ offsets, i64 n_chunks, int reverse_output)
+                  const u32 *__restrict__ offsets, i64 n_chunks, int reverse_output,
+                  int chunk_size)
 {
     __shared__ u32 running[kRadixWarps][kRadixBins];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -169,30 +182,41 @@ __global__ void __launch_bounds__(kThreads)
     if (chunk >= n_chunks) return;  // whole warp leaves together
     for (int d = lane; d < kRadixBins; d += 32) running[warp][d] = offsets[(i64)d * n_chunks + chunk];
     __syncwarp();
-    const i64 base = chunk * kRadixChunk;
+    const i64 base = chunk * chunk_size;
     const unsigned lt = (1u << lane) - 1u;
-    for (int g = 0; g < kRadixChunk / 32; ++g) {
-        i64 i = base + g * 32 + lane;
-        if (base + g * 32 >= n) break;  // uniform across the warp
-        bool active = i < n;
-        K key = active ? keys_in[i] : K(0);
-        V val = active ? vals_in[i] : V(0);
-        int d = active ? (int)((u32)(key >> shift) & 0xffu) : kRadixBins + lane;
-        unsigned peers = __match_any_sync(0xffffffffu, d);
-        u32 pos = 0;
-        if (active) pos = running[warp][d] + __popc(peers & lt);
-        __syncwarp();
-        if (active && (peers & lt) == 0) running[warp][d] += __popc(peers);
-        __syncwarp();
-        if (active) {
-            i64 p = reverse_output ? (n - 1 - (i64)pos) : (i64)pos;
-            keys_out[p] = key;
-            vals_out[p] = val;
+    for (int g0 = 0; g0 < chunk_size / 32; g0 += kRadixGroup) {
+        if (base + (i64)g0 * 32 >= n) break;  // uniform across the warp
+        // the loads of a whole group are in flight together; the replay below is in order
+        K key[kRadixGroup];
+        V val[kRadixGroup];
+#pragma unroll
+        for (int u = 0; u < kRadixGroup; ++u) {
+            const i64 i = base + (g0 + u) * 32 + lane;
+            const bool active = i < n;
+            key[u] = active ? keys_in[i] : K(0);
+            val[u] = active ? vals_in[i] : V(0);
+        }
+#pragma unroll
+        for (int u = 0; u < kRadixGroup; ++u) {
+            const i64 i = base + (g0 + u) * 32 + lane;
+            const bool active = i < n;
+            const int d = active ? (int)((u32)(key[u] >> shift) & 0xffu) : kRadixBins + lane;
+            const unsigned peers = __match_any_sync(0xffffffffu, d);
+            u32 pos = 0;
+            if (active) pos = running[warp][d] + __popc(peers & lt);
+            __syncwarp();
+            if (active && (peers & lt) == 0) running[warp][d] += __popc(peers);
+            __syncwarp();
+            if (active) {
+                const i64 p = reverse_output ? (n - 1 - (i64)pos) : (i64)pos;
+                keys_out[p] = key[u];
+                vals_out[p] = val[u];
+            }
         }
     }
 }
 
-static inline i64 radix_n_chunks(i64 n) { return (n + kRadixChunk - 1) / kRadixChunk; }
+static inline i64 radix_n_chunks(i64 n) { return (n + radix_chunk(n) - 1) / radix_chunk(n); }
 
 // scratch (in u32 elements) needed by one radix pass over n elements
 static inline size_t radix_scratch_u32(i64 n)
@@ -212,10 +236,11 @@ static inline void radix_pass(const K *keys_in, const V *vals_in, K *keys_out, V
     u32 *hist = scratch;
     u32 *scan_ws = scratch + h + 1;
     const int blocks = (int)((n_chunks + kRadixWarps - 1) / kRadixWarps);
-    radix_histogram<K><<<blocks, kThreads, 0, st>>>(keys_in, n, shift, hist, n_chunks);
+    const int chunk = radix_chunk(n);
+    radix_histogram<K><<<blocks, kThreads, 0, st>>>(keys_in, n, shift, hist, n_chunks, chunk);
     device_exclusive_scan<u32>(hist, hist, h, 0, scan_ws, st);
     radix_scatter<K, V><<<blocks, kThreads, 0, st>>>(keys_in, vals_in, keys_out, vals_out, n, shift,
-                                                     hist, n_chunks, reverse_output);
+                                                     hist, n_chunks, reverse_output, chunk);
 }
 
 // ---------------------------------------------------------------------------------

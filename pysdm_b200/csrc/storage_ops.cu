@@ -151,9 +151,13 @@ template <typename T, bool IsMax>
 __global__ void k_reduce_final(const T *__restrict__ partial, int n_partial,
                                const int *__restrict__ nan_flag, T *__restrict__ result)
 {
+    // one warp: strided pass over the partials, then a shuffle tree (min / max are
+    // order-independent)
+    T acc = partial[0];
+    for (int i = threadIdx.x; i < n_partial; i += 32) acc = red_op<T, IsMax>(acc, partial[i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc = red_op<T, IsMax>(acc, __shfl_xor_sync(0xffffffffu, acc, o));
     if (threadIdx.x == 0) {
-        T acc = partial[0];
-        for (int i = 1; i < n_partial; ++i) acc = red_op<T, IsMax>(acc, partial[i]);
         result[0] = acc;
         ((i64 *)result)[1] = (i64)(*nan_flag);
     }

@@ -291,6 +291,7 @@ __global__ void k_f64_sort_keys(const double *__restrict__ attr, u64 *__restrict
     i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     double v = attr[i];
+    if (v == 0.0) v = 0.0;  // -0.0 and +0.0 are ties for numpy
     u64 b = (u64)__double_as_longlong(v);
     if (v != v)
         b = ~(u64)0;  // every NaN last, like numpy
@@ -298,6 +299,119 @@ __global__ void k_f64_sort_keys(const double *__restrict__ attr, u64 *__restrict
         b = (b >> 63) ? ~b : (b | ((u64)1 << 63));
     keys[i] = b;
     vals[i] = i;
+}
+
+// Small arrays (the per-cell keys of one GPU's slab: a few 10^4 cells): the whole sort --
+// key construction, 8 stable passes, reversed output -- in ONE launch of one 1024-thread CTA.
+// The multi-kernel path above costs 5 launches per pass, ~30 us each way for 32768 keys, and
+// was a third of the GPU time of an adaptive sub-step (profiles/r1_config3_launches).
+// Per pass: warp-private digit histograms in shared memory (warp w owns a contiguous chunk),
+// exclusive scan over (digit-major, warp-minor), in-order replay of every chunk -- the same
+// stable construction as radix_histogram / radix_scatter.
+constexpr int kSmallSortThreads = 1024, kSmallSortWarps = kSmallSortThreads / 32;
+constexpr i64 kSmallSortMax = 65536;
+
+__global__ void __launch_bounds__(kSmallSortThreads)
+    k_sort_by_key_small(const double *__restrict__ attr, u64 *ka, i64 *va, u64 *kb, i64 *vb,
+                        i64 *__restrict__ idx, int n)
+{
+    __shared__ u32 hist[kRadixBins][kSmallSortWarps + 1];  // [digit][warp], padded
+    __shared__ u32 warp_sums[kSmallSortWarps];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    for (int i = tid; i < n; i += kSmallSortThreads) {  // k_f64_sort_keys
+        double v = attr[i];
+        if (v == 0.0) v = 0.0;  // -0.0 and +0.0 are ties for numpy
+        u64 b = (u64)__double_as_longlong(v);
+        if (v != v)
+            b = ~(u64)0;
+        else
+            b = (b >> 63) ? ~b : (b | ((u64)1 << 63));
+        ka[i] = b;
+        va[i] = i;
+    }
+    // contiguous chunk of warp w: [w * chunk, (w + 1) * chunk), chunk a multiple of 32
+    const int chunk = ((n + kSmallSortWarps - 1) / kSmallSortWarps + 31) / 32 * 32;
+    const int begin = warp * chunk, end = begin + chunk < n ? begin + chunk : n;
+    for (int p = 0; p < 8; ++p) {
+        const int shift = 8 * p;
+        for (int e = tid; e < kRadixBins * (kSmallSortWarps + 1); e += kSmallSortThreads)
+            (&hist[0][0])[e] = 0;
+        __syncthreads();  // also orders the previous pass's global writes before these reads
+        for (int i = begin + lane; i < end; i += 32)
+            atomicAdd(&hist[(u32)(ka[i] >> shift) & 0xffu][warp], 1u);
+        __syncthreads();
+        // exclusive scan of the 256 x 32 counts in (digit, warp) order: thread t owns the 8
+        // consecutive entries 8t .. 8t + 7 = digit t / 4, warps 8 (t % 4) ..
+        u32 c[8], sum = 0;
+        {
+            const int d = tid >> 2, w0 = (tid & 3) * 8;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                c[u] = hist[d][w0 + u];
+                sum += c[u];
+            }
+        }
+        u32 inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const u32 t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) warp_sums[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            const u32 w = warp_sums[lane];
+            u32 winc = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const u32 t = __shfl_up_sync(0xffffffffu, winc, o);
+                if (lane >= o) winc += t;
+            }
+            warp_sums[lane] = winc - w;
+        }
+        __syncthreads();
+        {
+            u32 ex = warp_sums[warp] + inc - sum;
+            const int d = tid >> 2, w0 = (tid & 3) * 8;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                hist[d][w0 + u] = ex;
+                ex += c[u];
+            }
+        }
+        __syncthreads();
+        // in-order replay of my chunk; hist[d][warp] is the running output offset
+        const bool last = p == 7;
+        for (int i0 = begin; i0 < end; i0 += 32) {
+            const int i = i0 + lane;
+            const bool active = i < end;
+            const u64 key = active ? ka[i] : 0;
+            const i64 val = active ? va[i] : 0;
+            const int d = active ? (int)((u32)(key >> shift) & 0xffu) : kRadixBins + lane;
+            const unsigned peers = __match_any_sync(0xffffffffu, d);
+            u32 pos = 0;
+            if (active) pos = hist[d][warp] + __popc(peers & lt);
+            __syncwarp();
+            if (active && (peers & lt) == 0) hist[d][warp] += __popc(peers);
+            __syncwarp();
+            if (active) {
+                if (last) {
+                    idx[n - 1 - (int)pos] = val;  // [::-1]
+                } else {
+                    kb[pos] = key;
+                    vb[pos] = val;
+                }
+            }
+        }
+        __syncthreads();  // every warp is done with hist[] and with this pass's input
+        u64 *t = ka;
+        ka = kb;
+        kb = t;
+        i64 *tv = va;
+        va = vb;
+        vb = tv;
+    }
 }
 
 static size_t sort_by_key_ws_bytes(i64 n)
@@ -328,6 +442,10 @@ PYSDM_EXPORT int pysdm_b200_sort_by_key(i64 *idx, const double *attr, i64 n, voi
     i64 *vb = (i64 *)w;
     w += align_up(sizeof(i64) * (size_t)n);
     u32 *scratch = (u32 *)w;
+    if (n <= kSmallSortMax) {
+        k_sort_by_key_small<<<1, kSmallSortThreads, 0, st>>>(attr, ka, va, kb, vb, idx, (int)n);
+        return LAUNCH_CHECK();
+    }
     k_f64_sort_keys<<<grid_for(n), kThreads, 0, st>>>(attr, ka, va, n);
     for (int p = 0; p < 8; ++p) {
         const bool last = p == 7;

@@ -199,6 +199,20 @@ def test_sort_by_key_and_cell_id(be, golden_methods, tag):
     np.testing.assert_array_equal(out, c["out"])
 
 
+@pytest.mark.parametrize("n", (1, 2, 33, 1000, 32768, 65536, 65537, 300000))
+def test_sort_by_key_sizes(be, n):
+    """`argsort(kind="stable")[::-1]` (index_methods.py:46-48) at the sizes where the CUDA path
+    switches algorithm (one-CTA sort up to 65536 keys, multi-kernel radix sort above), with
+    heavy ties (dt_left is mostly 0 or dt), signed zeros, negatives, infinities and NaN"""
+    rng = np.random.default_rng(n)
+    keys = rng.choice([0.0, 5.0, -0.0, 2.5, np.inf, -np.inf, np.nan], n)
+    some = rng.random(n) < 0.3
+    keys[some] = rng.normal(0, 3, int(some.sum()))
+    out = np.full(n, -1, np.int64)
+    be.sort_by_key(out, keys)
+    np.testing.assert_array_equal(out, np.argsort(keys, kind="stable")[::-1])
+
+
 # ---- whole time steps ---------------------------------------------------------------------
 def make_oracle_from_scenario(s, name, be=orc):
     kw = dict(SCENARIO_KW[name])

@@ -207,9 +207,17 @@ typedef struct pysdm_b200_fused_args {
                                    zeroes gate[0] when it has removed the zero-multiplicity SDs. */
     int64_t epoch;              /* != 0, different for consecutive launches */
     uint32_t philox_round_keys[20]; /* filled in by the launcher from `seed` */
+    int64_t shuffle_only;       /* set by pysdm_b200_shuffle_local_batched: stop after the shuffle */
 } pysdm_b200_fused_args;
 
 int64_t pysdm_b200_fused_max_cell_size(void);
+/* shuffle_local (index_methods.py:32-44) for populations whose cells all hold at most
+ * max_cell_size <= pysdm_b200_fused_max_cell_size() super-droplets: the staging + swap-chain
+ * phases of the fused step alone (shared memory, one launch) instead of the general
+ * five-kernel replay of pysdm_b200_shuffle_local.  In place; same result bit for bit. */
+int pysdm_b200_shuffle_local_batched(int64_t *idx, const double *u01, const int64_t *cell_start,
+                                     int64_t n_cell, int64_t n_sd, int64_t max_cell_size,
+                                     int64_t *status, void *stream);
 int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *host_args, void *stream);
 
 /* ---- terminal velocities: methods/terminal_velocity_methods.py ----------------------- */

@@ -54,6 +54,7 @@ SIGNATURES = {
     "pysdm_b200_max_cell_size": (INT, (P, I64, P, P, P)),
     "pysdm_b200_fused_max_cell_size": (I64, ()),
     "pysdm_b200_fused_collision_step": (INT, (P, P)),
+    "pysdm_b200_shuffle_local_batched": (INT, (P, P, P, I64, I64, I64, P, P)),
     "pysdm_b200_interpolation": (INT, (P, P, I64, F64, P, P, P)),
     "pysdm_b200_terminal_velocity_rogers_yau": (INT, (P, P, I64, F64, F64, F64, F64, F64, P)),
     "pysdm_b200_power_series": (INT, (P, P, I64, I64, P, P, P)),
@@ -98,7 +99,7 @@ class FusedArgs(ctypes.Structure):
         + [(n, F64) for n in ("timestep", "dv", "rho_w", "substeps", "kernel_a", "kernel_b")]
         + [("kernel", ctypes.c_int32), ("reserved", ctypes.c_int32), ("max_cell_size", I64),
            ("nf_slot", P), ("refresh_nf", I64), ("gate", P), ("epoch", I64),
-           ("philox_round_keys", U32 * 20)])
+           ("philox_round_keys", U32 * 20), ("shuffle_only", I64)])
 
 
 KERNELS = {"Golovin": 0, "ConstantK": 1, "Linear": 2}

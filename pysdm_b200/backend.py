@@ -14,6 +14,8 @@ NotImplementedError, as ThrustRTC does for chemistry/seeding/deposition.
 No CPU fallback: constructing `B200` without the CUDA library or a CUDA device fails.
 """
 
+import weakref
+
 import numpy as np
 import torch
 
@@ -74,9 +76,17 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
     def shuffle_global(idx, length, u01):  # :22-30
         m.shuffle_global(idx, int(length), u01)
 
+    # what the last sort by cell learnt about `cell_start` (keyed by its device pointer): the
+    # working length and the largest cell, so that shuffle_local needs no device sync and
+    # can pick the one-launch shuffle for populations of small cells
+    _cell_start_facts = {}  # id(tensor) -> (weakref to the tensor, length, largest cell)
+
     @staticmethod
     def shuffle_local(idx, u01, cell_start):  # :32-44
-        m.shuffle_local(idx, u01, cell_start)
+        ref, length, max_cell = B200._cell_start_facts.get(id(cell_start), (None, None, None))
+        if ref is None or ref() is not cell_start:  # not (or no longer) the tensor that was sorted
+            length = max_cell = None
+        m.shuffle_local(idx, u01, cell_start, length, max_cell)
 
     @staticmethod
     def sort_by_key(idx, attr):  # :46-48
@@ -102,6 +112,11 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
                 m.counting_sort_by_cell_id(self.tmp_idx.data, idx.data, cell_id.data,
                                            cell_idx.data, len(idx), cell_start.data)
                 idx.data, self.tmp_idx.data = self.tmp_idx.data, idx.data
+                facts = B200._cell_start_facts
+                for key in [k for k, v in facts.items() if v[0]() is None]:
+                    del facts[key]  # tensors that are gone
+                facts[id(cell_start.data)] = (weakref.ref(cell_start.data), len(idx),
+                                              m.max_cell_size(cell_start.data))
 
         assert cell_start_len >= 1
         return CellCaretaker()

@@ -198,7 +198,9 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         if local:
             cell_start = self.get_cell_start()
             # the reference walks every cell of cell_start, also beyond a cut working length
-            m.shuffle_local(self.idx, u01, cell_start, self.sorted_length)
+            if self.max_cell is None:
+                self.max_cell = m.max_cell_size(self.cell_start)
+            m.shuffle_local(self.idx, u01, cell_start, self.sorted_length, self.max_cell)
         else:
             m.shuffle_global(self.idx, self.length, u01)
             self.sorted = False

@@ -276,9 +276,10 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     const bool rho_ok = a.reserved != 0;  // host-checked precondition of div_by
 
     // ---- tail: pair slots beyond the working length keep `0 * norm_factor` ------------
-    for (i64 d = n_pairs_active + (i64)blockIdx.x * kFusedThreads + tid; d < a.n_sd / 2;
-         d += (i64)gridDim.x * kFusedThreads)
-        a.gamma[d] = prob_nopair * a.nf_slot[d] / a.substeps;
+    if (!a.shuffle_only)
+        for (i64 d = n_pairs_active + (i64)blockIdx.x * kFusedThreads + tid; d < a.n_sd / 2;
+             d += (i64)gridDim.x * kFusedThreads)
+            a.gamma[d] = prob_nopair * a.nf_slot[d] / a.substeps;
 
     const i64 batch = (i64)blockIdx.x * G::kGroups + group;
     const i64 c0 = batch * a.cells_per_batch;
@@ -431,7 +432,8 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     for (int c = gt; c < ncb; c += G::kSize) {
         const int s = cs[c], e = cs[c + 1];
         i64 cid = 0;
-        if (e > s) cid = a.cell_id[sd[phys(s)]];  // issued now, consumed after the chain
+        if (e > s && !a.shuffle_only)
+            cid = a.cell_id[sd[phys(s)]];  // issued now, consumed after the chain
         // positions of a 64-block are contiguous in the skewed layout: walk block by block
         // with unit stride (the bookkeeping of the skew was half of the chain's instructions)
         int i = e - 1;
@@ -453,6 +455,11 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
         cidv[c] = cid;
     }
     group_sync<kWarp>();
+
+    if (a.shuffle_only) {  // pysdm_b200_shuffle_local_batched: the permuted order, nothing else
+        for (int lp = lo + gt; lp < P; lp += G::kSize) a.idx_out[base_al + lp] = (i64)sd[phys(lp)];
+        return;
+    }
 
     // ---- phase 4: two pair slots per thread and iteration ---------------------------------
     const double *mass = a.attributes + a.mass_row * a.n_sd;
@@ -725,4 +732,32 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
     case KERNEL_LINEAR: return dispatch_fused<KERNEL_LINEAR>(a, n_batches, philox, warp, aggregate, st);
     default: return (int)cudaErrorInvalidValue;
     }
+}
+
+PYSDM_EXPORT int pysdm_b200_shuffle_local_batched(i64 *idx, const double *u01, const i64 *cell_start,
+                                                  i64 n_cell, i64 n_sd, i64 max_cell_size,
+                                                  i64 *status, void *stream)
+{
+    if (n_sd <= 0 || n_sd >= ((i64)1 << 32) || n_cell <= 0) return (int)cudaErrorInvalidValue;
+    if (max_cell_size > kCtaPos) return (int)cudaErrorInvalidConfiguration;
+    FusedArgs a = {};
+    a.idx_in = idx;
+    a.idx_out = idx;  // in place: a batch stages its whole range before it writes
+    a.u01 = u01;
+    a.cell_start = cell_start;
+    a.status = status;
+    a.n_sd = n_sd;
+    a.n_cell = n_cell;
+    a.substeps = 1.0;
+    a.shuffle_only = 1;
+    const i64 mcs = max_cell_size < 1 ? 1 : max_cell_size;
+    const bool warp = mcs <= kWarpPos;
+    i64 cpb = (warp ? kWarpPos : kCtaPos) / mcs;
+    const i64 cap = warp ? kWarpCells : kCtaCells;
+    if (cpb > cap) cpb = cap;
+    a.cells_per_batch = cpb;
+    const i64 n_batches = (n_cell + cpb - 1) / cpb;
+    cudaStream_t st = (cudaStream_t)stream;
+    return warp ? launch_fused<KERNEL_CONSTANT_K, false, true, false>(a, n_batches, st)
+                : launch_fused<KERNEL_CONSTANT_K, false, false, false>(a, n_batches, st);
 }

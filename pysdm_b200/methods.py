@@ -79,9 +79,23 @@ def shuffle_global(idx, length, u01):
                                         _stream()), "shuffle_global")
 
 
-def shuffle_local(idx, u01, cell_start, length=None):
-    """`length` = cell_start[-1]; pass it when known on the host to avoid a device sync"""
+_STATUS = {}
+
+
+def shuffle_local(idx, u01, cell_start, length=None, max_cell=None):
+    """`length` = cell_start[-1]; pass it when known on the host to avoid a device sync.
+    `max_cell` = size of the largest cell, when the host knows it: populations of small cells
+    then take the one-launch shared-memory shuffle instead of the general replay"""
     lib = _lib.load()
+    if (max_cell is not None and max_cell <= lib.pysdm_b200_fused_max_cell_size()
+            and idx.numel() < 2 ** 32 and u01.numel() >= idx.numel()):
+        status = _STATUS.get(idx.device)
+        if status is None:
+            status = _STATUS[idx.device] = torch.zeros(1, dtype=torch.int64, device=idx.device)
+        check(lib.pysdm_b200_shuffle_local_batched(
+            _pi(idx), _pf(u01), _pi(cell_start), cell_start.numel() - 1, idx.numel(),
+            int(max_cell), _pi(status), _stream()), "shuffle_local_batched")
+        return
     if length is None:
         length = int(cell_start[-1].item())
     nbytes = lib.pysdm_b200_shuffle_workspace_bytes(int(length))

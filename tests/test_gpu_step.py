@@ -249,6 +249,33 @@ def test_full_size_properties_and_fused_equals_methods():
     assert sims[0].n_fused_steps == 2 and sims[1].n_fused_steps == 0
 
 
+@pytest.mark.parametrize("mean, n_cell", ((3, 2000), (128, 300), (3000, 4), (700, 1)))
+def test_batched_shuffle_local_equals_oracle(mean, n_cell):
+    """pysdm_b200_shuffle_local_batched (the shuffle phases of the fused kernel alone, what the
+    backend uses when the sort told it that every cell is small) against the oracle's serial
+    shuffle_local, ragged cells incl. empty ones, unaligned u01 view as `optimized_random` makes"""
+    import torch  # pylint: disable=import-outside-toplevel
+
+    from oracle import sdm_oracle as orc  # pylint: disable=import-outside-toplevel
+    from pysdm_b200 import methods as m  # pylint: disable=import-outside-toplevel
+
+    rng = np.random.default_rng(mean)
+    sizes = rng.poisson(mean, n_cell)
+    sizes[rng.integers(0, n_cell, max(1, n_cell // 10))] = 0
+    cell_start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    n = int(cell_start[-1])
+    n_sd = n + 5  # positions beyond the working length stay untouched
+    idx = rng.permutation(n_sd).astype(np.int64)
+    for shift in (0, 1):
+        u_all = rng.random(n_sd + shift)
+        expect = idx.copy()
+        orc.shuffle_local(expect, np.ascontiguousarray(u_all[shift:]), cell_start)
+        d_idx = torch.from_numpy(idx.copy()).cuda()
+        d_u = torch.from_numpy(u_all).cuda()[shift:]
+        m.shuffle_local(d_idx, d_u, torch.from_numpy(cell_start).cuda(), n, int(sizes.max()))
+        np.testing.assert_array_equal(d_idx.cpu().numpy(), expect)
+
+
 class _Host:  # pylint: disable=too-few-public-methods
     """numpy face of a DeviceCollision, shaped like OracleCollision for compare_states"""
 

@@ -196,6 +196,10 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
                          "use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
     if world > 1:
+        # stdout carries exactly one JSON line: keep NCCL's version banner (printed to stdout
+        # under NCCL_DEBUG=VERSION) out of it; an explicit INFO / TRACE setting is respected
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():

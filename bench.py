@@ -196,10 +196,9 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
                          "use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
     if world > 1:
-        # stdout carries exactly one JSON line: keep NCCL's version banner (printed to stdout
-        # under NCCL_DEBUG=VERSION) out of it; an explicit INFO / TRACE setting is respected
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # stdout carries exactly one JSON line: NCCL's version banner and any other NCCL_DEBUG
+        # output (which NCCL writes to stdout) go to stderr instead
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():

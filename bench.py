@@ -191,14 +191,16 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly one JSON line: whatever native libraries write to fd 1 during the
+    # run (NCCL prints its version banner there) goes to stderr instead
+    sys.stdout.flush()
+    stdout_fd = os.dup(1)
+    os.dup2(2, 1)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback); "
                          "use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
     if world > 1:
-        # stdout carries exactly one JSON line: NCCL's version banner and any other NCCL_DEBUG
-        # output (which NCCL writes to stdout) go to stderr instead
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -269,7 +271,10 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
         if not args.no_cpu_baseline and world == 1:
             r = cpu_run(args, 3, 1)
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.dup2(stdout_fd, 1)
+        print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
     if world > 1:
         dist.destroy_process_group()
 

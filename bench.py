@@ -47,6 +47,8 @@ def parse():
                     help="bounded CPU sample: super-droplets per CPU step (log2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-numba", action="store_true",
+                    help="skip timing the reference's own Numba backend next to the port")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--e2e-stripes", type=int, default=4)
     return ap.parse_args()
@@ -110,6 +112,57 @@ def cpu_run(args, steps, warmup):
     }
 
 
+def numba_run(args, steps=2):
+    """the reference's OWN Numba CPU backend (unmodified PySDM from baseline/_ref, its stock
+    Builder / Particulator / Coalescence path) on the same bounded sample, when it is importable
+    on this box (numba + the install under baseline/_ref); reported next to the port, never used
+    as the denominator of anything.  Returns a dict, or {"unavailable": why}."""
+    ref = next((p for p in (os.path.join(ROOT, "baseline", "_ref"), "/root/reference")
+                if os.path.isdir(os.path.join(p, "PySDM"))), None)
+    if ref is None:
+        return {"unavailable": "no PySDM install under baseline/_ref"}
+    try:
+        os.environ.setdefault("CI", "1")  # PySDM's own switch: do not import ThrustRTC
+        sys.path.insert(0, os.path.join(ROOT, "oracle", "refshims"))  # pint / chempy stand-ins
+        sys.path.insert(1, ref)
+        np.NaN = np.nan  # the reference predates NumPy 2
+        import numba  # pylint: disable=import-outside-toplevel
+        from PySDM import Builder, Formulae  # pylint: disable=import-outside-toplevel
+        from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+        from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+        from PySDM.dynamics.collisions.collision_kernels import Golovin  # pylint: disable=import-outside-toplevel
+        from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
+        from PySDM.impl.mesh import Mesh  # pylint: disable=import-outside-toplevel
+
+        n_sd = 1 << min(args.cpu_log2_n_sd, args.log2_n_sd)
+        pop = population(n_sd, args.sd_per_cell, 0)
+        env = Box(dv=1.0, dt=1.0)
+        env.mesh = Mesh((pop["n_cell"],), size=(pop["n_cell"],), dv=1.0)
+        builder = Builder(n_sd=n_sd, backend=CPU(Formulae(seed=44)), environment=env)
+        builder.add_dynamic(Coalescence(collision_kernel=Golovin(b=GOLOVIN_B), adaptive=False,
+                                        croupier="local"))
+        particulator = builder.build(products=(), attributes={
+            "multiplicity": pop["multiplicity"], "volume": pop["water_mass"] / RHO_W,
+            "cell id": pop["cell_id"]})
+        particulator.run(1)  # JIT
+        ncpu, best = numba.config.NUMBA_NUM_THREADS, None
+        for threads in sorted({1, ncpu}):
+            numba.set_num_threads(threads)
+            particulator.run(1)
+            t0 = time.perf_counter()
+            particulator.run(steps)
+            dt = (time.perf_counter() - t0) / steps
+            if best is None or dt < best[1]:
+                best = (threads, dt)
+        return {"value": n_sd / best[1], "unit": "SD-steps/s", "cores": best[0],
+                "kind": "reference", "ms_per_step": best[1] * 1e3,
+                "sample": f"{steps} steps of 2^{int(np.log2(n_sd))} SDs ({args.sd_per_cell}/cell), "
+                          f"PySDM Numba backend (baseline/_ref, stock Builder/Coalescence path), "
+                          f"best of {sorted({1, ncpu})} numba threads"}
+    except Exception as exc:  # pylint: disable=broad-except
+        return {"unavailable": f"{type(exc).__name__}: {exc}"[:200]}
+
+
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -127,6 +180,8 @@ def reference_arm(args):
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if not args.no_numba:
+        line["cpu_baseline"]["numba_backend"] = numba_run(args)
     print(json.dumps(line))
 
 
@@ -271,6 +326,8 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
         if not args.no_cpu_baseline and world == 1:
             r = cpu_run(args, 3, 1)
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            if not args.no_numba:
+                line["cpu_baseline"]["numba_backend"] = numba_run(args)
         sys.stdout.flush()
         os.dup2(stdout_fd, 1)
         print(json.dumps(line), flush=True)

@@ -7,12 +7,18 @@ The CUDA library (libpysdm_b200.so, built in-tree by `python -m pysdm_b200.build
 mandatory: there is no CPU fallback.
 """
 
-__all__ = ("B200",)
+__all__ = ("B200", "FusedCoalescence")
 
 
-def __getattr__(name):  # lazy: importing the package must not need torch/CUDA
+def __getattr__(name):  # lazy: importing the package must not need torch/CUDA (or PySDM)
     if name == "B200":
         from .backend import B200  # pylint: disable=import-outside-toplevel
 
         return B200
+    if name == "FusedCoalescence":  # PySDM's Coalescence with step() on the fused kernel
+        from .dynamics import make_fused_coalescence  # pylint: disable=import-outside-toplevel
+
+        cls = make_fused_coalescence()
+        globals()[name] = cls
+        return cls
     raise AttributeError(name)

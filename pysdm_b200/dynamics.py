@@ -1,0 +1,118 @@
+"""`FusedCoalescence`: PySDM's `Coalescence` dynamic with `step()` mapped onto the one-launch
+fused kernel (csrc/fused.cu) -- for users of the unchanged PySDM orchestration
+(`Builder`, `Particulator`, attributes, products) who want the collision step at the speed
+`bench.py` measures instead of ~15 backend calls per step:
+
+    from pysdm_b200 import B200, FusedCoalescence
+    builder = Builder(n_sd, backend=B200(), environment=...)
+    builder.add_dynamic(FusedCoalescence(collision_kernel=Golovin(b=1.5e3)))
+
+It derives from the reference's own class (PySDM/dynamics/collisions/collision.py:46-290,
+`Coalescence` :293-330), registers under the same name ("Collision"), allocates the same
+storages, and overrides `step()` only: when the configuration is one the fused kernel
+covers -- B200 backend, non-adaptive, "local" croupier, Golovin / ConstantK / Linear kernel,
+no breakup, every cell within the fused kernel's size limit, `optimized_random` off -- one
+launch replaces the sequence `Collision.step` issues (:196-234) and writes every storage
+that sequence writes (idx, pair flags, gamma, multiplicities, attributes, norm factors, rate
+counters, `healthy`), bit for bit (tests/test_gpu_pysdm_backend.py).  Anything else falls
+through to the reference's `step()` and the method-level kernels.
+"""
+
+import torch
+
+from . import methods as m
+from .random import Random
+
+_KERNELS = {"Golovin": lambda k: (0.0, k.b), "ConstantK": lambda k: (k.a, 0.0),
+            "Linear": lambda k: (k.a, k.b)}
+
+
+def make_fused_coalescence():
+    """builds the class lazily: importing pysdm_b200 must not need PySDM"""
+    from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+
+    from .backend import B200  # pylint: disable=import-outside-toplevel
+
+    class FusedCoalescence(Coalescence):
+        def __init__(self, *args, **kwargs):
+            super().__init__(*args, **kwargs)
+            self.n_fused_steps = 0
+            self._nf_slot = self._status = self._nf_facts = None
+
+        def register(self, builder):
+            super().register(builder)
+            dev = self.gamma.data.device
+            self._nf_slot = torch.full((self.particulator.n_sd // 2,), float("nan"),
+                                       dtype=torch.float64, device=dev)
+            self._status = torch.zeros(1, dtype=torch.int64, device=dev)
+
+        def _fused_plan(self):
+            """(kernel name, a, b, facts of the current sort) or None"""
+            part = self.particulator
+            name = type(self.collision_kernel).__name__
+            if (not isinstance(part.backend, B200) or self.adaptive or self.enable_breakup
+                    or self.croupier != "local" or name not in _KERNELS
+                    or self.rnd_opt_coll.optimized_random or part.n_sd >= 2 ** 32):
+                return None
+            cell_start = part.attributes.cell_start  # sorts by cell when needed
+            facts = B200._cell_start_facts.get(id(cell_start.data))  # pylint: disable=protected-access
+            if facts is None or facts[0]() is not cell_start.data:
+                return None
+            if facts[2] > m.fused_max_cell_size():
+                return None
+            return (name, *_KERNELS[name](self.collision_kernel), facts)
+
+        def step(self):
+            plan = self._fused_plan()
+            if plan is None:
+                super().step()
+                return
+            name, kernel_a, kernel_b, facts = plan
+            part, attrs = self.particulator, self.particulator.attributes
+            # the reference reaches these through the same name-mangled handles
+            # (PySDM/particulator.py:174-176)
+            idx = attrs._ParticleAttributes__idx  # pylint: disable=protected-access
+            healthy = attrs._ParticleAttributes__healthy_memory  # pylint: disable=protected-access
+            caretaker = attrs._ParticleAttributes__cell_caretaker  # pylint: disable=protected-access
+            keys = attrs._ParticleAttributes__extensive_keys  # pylint: disable=protected-access
+            mass_row = keys.get("signed water mass", keys.get("water mass"))
+            if mass_row is None:
+                super().step()
+                return
+            rnd = self.rnd_opt_coll.rnd
+            if isinstance(rnd, Random):  # device Philox: generated inside the kernel
+                kw = {"seed": rnd.seed, "call_u01": rnd.call, "call_rand": rnd.call + 1}
+                rnd.call += 2
+                self.rnd_opt_coll.substep += 1
+            else:  # injected uniforms (parity runs with the Numba backend's stream)
+                pairs_rand, rand = self.rnd_opt_coll.get_random_arrays()
+                kw = {"u01": pairs_rand.data, "rand": rand.data}
+            length = len(idx)
+            ext = attrs.get_extensive_attribute_storage()
+            substeps = self._Collision__substeps  # pylint: disable=no-member
+            err = m.fused_collision_step(
+                idx_in=idx.data, idx_out=caretaker.tmp_idx.data, cell_start=attrs.cell_start.data,
+                cell_idx=attrs.cell_idx.data, cell_id_=attrs["cell id"].data,
+                multiplicity=attrs["multiplicity"].data, attributes=ext.data,
+                is_first_in_pair=self.is_first_in_pair.indicator.data, gamma=self.gamma.data,
+                norm_factor=self.norm_factor_temp.data, collision_rate=self.collision_rate.data,
+                collision_rate_deficit=self.collision_rate_deficit.data,
+                coalescence_rate=self.coalescence_rate.data, healthy=healthy.data,
+                status=self._status, length=length, max_cell=facts[2], kernel=name,
+                kernel_a=kernel_a, kernel_b=kernel_b, timestep=part.dt, dv=part.mesh.dv,
+                rho_w=part.backend.rho_w, substeps=substeps, mass_row=mass_row,
+                nf_slot=self._nf_slot, refresh_nf=self._nf_facts is not facts, **kw)
+            m.check(err, "fused_collision_step")
+            self._nf_facts = facts
+            if length < idx.data.numel():  # flagged positions beyond the working length stay
+                caretaker.tmp_idx.data[length:] = idx.data[length:]
+            idx.data, caretaker.tmp_idx.data = caretaker.tmp_idx.data, idx.data
+            self.is_first_in_pair.length = length
+            self.n_fused_steps += 1
+            # Particulator.collision_coalescence_breakup, PySDM/particulator.py:210-213
+            attrs.sanitize()
+            attrs.mark_updated("multiplicity")
+            for key in attrs.get_extensive_attribute_keys():
+                attrs.mark_updated(key)
+
+    return FusedCoalescence

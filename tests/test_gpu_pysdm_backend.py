@@ -38,9 +38,12 @@ def pysdm():
     return PySDM
 
 
-def build(pysdm, backend, *, n_sd, grid, dv, dt, attributes, dynamic_kw, kernel_b=1.5e3):
+def build(pysdm, backend, *, n_sd, grid, dv, dt, attributes, dynamic_kw, kernel_b=1.5e3,
+          fused_dynamic=False):
     from PySDM import Builder  # pylint: disable=import-outside-toplevel
     from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+    if fused_dynamic:
+        from pysdm_b200 import FusedCoalescence as Coalescence  # pylint: disable=import-outside-toplevel
     from PySDM.dynamics.collisions.collision_kernels import Golovin  # pylint: disable=import-outside-toplevel
     from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
     from PySDM.impl.mesh import Mesh  # pylint: disable=import-outside-toplevel
@@ -131,6 +134,56 @@ def test_b200_backend_equals_numba_backend(pysdm, case):
             np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
         collided = int(b["coalescence_rate"].sum())
     assert collided > 0
+
+
+@pytest.mark.parametrize("host_rng", (True, False))
+@pytest.mark.parametrize("case", ("local", "substeps", "box", "global"))
+def test_fused_coalescence_dynamic(pysdm, case, host_rng):
+    """`pysdm_b200.FusedCoalescence` (PySDM's Coalescence with step() on the one-launch fused
+    kernel) inside the unmodified PySDM orchestration.  host_rng=True: against the reference's
+    Numba backend with the stock dynamic, same uniforms.  host_rng=False: against the stock
+    dynamic on the B200 backend (method-level kernels), same device Philox stream.  Everything
+    bit-identical after every step; the "global" croupier is not covered by the fused kernel
+    and must fall through to the reference's step()."""
+    from PySDM import Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200  # pylint: disable=import-outside-toplevel
+
+    c = CASES[case]
+    n_sd, n_cell = c["n_sd"], int(np.prod(c["grid"]))
+    rng = np.random.default_rng(98)
+    attributes = {
+        "multiplicity": rng.integers(1, 5, n_sd).astype(np.int64),
+        "volume": rng.exponential(4.0 / 3 * np.pi * (30.531e-6) ** 3, n_sd),
+        "cell id": rng.integers(0, n_cell, n_sd).astype(np.int64),
+    }
+    common = dict(n_sd=n_sd, grid=c["grid"], dv=c["dv"], dt=1.0, attributes=attributes,
+                  dynamic_kw=c["kw"])
+    formulae = dict(fastmath=False, seed=4321)
+    ref_backend = CPU(Formulae(**formulae)) if host_rng else B200(Formulae(**formulae))
+    ref = build(pysdm, ref_backend, **common)
+    sut = build(pysdm, B200(Formulae(**formulae), host_rng=host_rng), fused_dynamic=True, **common)
+    for step in range(8):
+        ref.run(1)
+        sut.run(1)
+        a, b = snapshot(sut), snapshot(ref)
+        n = b["length"]
+        assert a["length"] == n, f"step {step}: length"
+        np.testing.assert_array_equal(a["idx"][:n], b["idx"][:n], f"step {step}: idx")
+        np.testing.assert_array_equal(a["flag"][:n], b["flag"][:n], f"step {step}: flag")
+        np.testing.assert_array_equal(a["multiplicity"], b["multiplicity"])
+        assert_same_f64(a["attributes"], b["attributes"], f"step {step}: attributes")
+        assert_same_f64(a["gamma"], b["gamma"], f"step {step}: gamma")
+        for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate"):
+            np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
+        # derived attributes are recomputed from what the fused step wrote
+        np.testing.assert_array_equal(sut.attributes["volume"].to_ndarray(),
+                                      ref.attributes["volume"].to_ndarray())
+    dyn = sut.dynamics["Collision"]
+    expected = 0 if case == "global" else 8 * c["kw"].get("substeps", 1)
+    assert dyn.n_fused_steps == expected
+    assert int(snapshot(ref)["coalescence_rate"].sum()) > 0
 
 
 # ---- configs 2 and 3 of BASELINE.json in miniature: gravitational kernels with hydrodynamic

@@ -27,8 +27,10 @@ os.environ.setdefault("CI", "1")
 np.NaN = np.nan
 
 
-def dynamics(config):
+def dynamics(config, fused=False):
     from PySDM.dynamics import Coalescence, Collision
+    if fused:
+        from pysdm_b200 import FusedCoalescence as Coalescence
     from PySDM.dynamics.collisions.breakup_efficiencies import ConstEb
     from PySDM.dynamics.collisions.breakup_fragmentations import Straub2010Nf
     from PySDM.dynamics.collisions.coalescence_efficiencies import Straub2010Ec
@@ -37,6 +39,8 @@ def dynamics(config):
 
     if config == 0:  # Shima et al. 2009 box
         return Coalescence(collision_kernel=Golovin(b=1.5e3), adaptive=False)
+    if config == 4:  # bench.py's workload (configs[4]) through the PySDM orchestration
+        return Coalescence(collision_kernel=Golovin(b=1.5e3), adaptive=False, croupier="local")
     if config == 1:  # Berry 1967 box
         return Coalescence(collision_kernel=Hydrodynamic(), adaptive=True,
                            dt_coal_range=(0.1, 100.0))
@@ -61,6 +65,9 @@ SETUP = {
     # per-GPU share of configs[3]: 32768 cells of 128 SDs, dv of one cell of the 1.5 km / 512 grid
     3: dict(name="Sc-rain collision step, Geometric + adaptive, 2^22 SDs in 32768 cells", log2=22,
             dt=5.0, dv=(1500 / 512) ** 2, r0=10e-6, norm=None, fkw={}, sd_per_cell=128),
+    4: dict(name="Golovin multi-cell coalescence, 2^24 SDs in 2^17 cells (bench.py workload)",
+            log2=24, dt=1.0, dv=1.0, r0=30.531e-6, norm=None, fkw={}, sd_per_cell=128,
+            multiplicity=2 ** 20),
 }
 
 
@@ -80,15 +87,17 @@ def run(config, backend_name, steps, log2=None):
         n_cell = n_sd // c["sd_per_cell"]
         env.mesh = Mesh((n_cell,), size=(n_cell,), dv=c["dv"])
         # ~100 droplets / cm^3 in every cell, lognormal-ish radii around r0
-        volume = 4 / 3 * np.pi * (c["r0"] * np.exp(0.47 * rng.standard_normal(n_sd))) ** 3
+        if "multiplicity" not in c:
+            volume = 4 / 3 * np.pi * (c["r0"] * np.exp(0.47 * rng.standard_normal(n_sd))) ** 3
         attributes = {"volume": volume, "cell id": np.arange(n_sd, dtype=np.int64) // c["sd_per_cell"],
-                      "multiplicity": np.full(n_sd, int(100e6 * c["dv"] / c["sd_per_cell"]),
-                                              dtype=np.int64)}
+                      "multiplicity": np.full(
+                          n_sd, c.get("multiplicity", int(100e6 * c["dv"] / c["sd_per_cell"])),
+                          dtype=np.int64)}
     else:
         attributes = {"volume": volume, "multiplicity": np.full(
             n_sd, max(1, int(c["norm"] / n_sd)), dtype=np.int64)}
     formulae = Formulae(seed=44, **c["fkw"])
-    if backend_name == "B200":
+    if backend_name.startswith("B200"):  # "B200F": FusedCoalescence instead of Coalescence
         from pysdm_b200 import B200
 
         backend = B200(formulae)
@@ -97,11 +106,11 @@ def run(config, backend_name, steps, log2=None):
 
         backend = CPU(formulae)
     builder = Builder(n_sd=n_sd, backend=backend, environment=env)
-    builder.add_dynamic(dynamics(config))
+    builder.add_dynamic(dynamics(config, fused=backend_name == "B200F"))
     particulator = builder.build(attributes=attributes, products=())
     particulator.run(2)  # warm-up (JIT / workspaces)
     sync = (lambda: None)
-    if backend_name == "B200":
+    if backend_name.startswith("B200"):
         import torch
 
         sync = torch.cuda.synchronize
@@ -130,4 +139,4 @@ if __name__ == "__main__":
     a = ap.parse_args()
     for cfg in (int(x) for x in a.configs.split(",")):
         for be in a.backends.split(","):
-            run(cfg, be, a.steps if be == "B200" else a.cpu_steps, a.log2)
+            run(cfg, be, a.steps if be.startswith("B200") else a.cpu_steps, a.log2)

@@ -478,7 +478,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
 
         // stage A: find_pairs (pair_methods.py:38-41, :55) for my positions, pair members
         bool has[2], dflt[2];
-        int pf[2], pcell[2];
+        int pf[2];
         u32 j[2], k[2];
         i64 nj[2], nk[2];
         double mj[2], mk[2], nf[2];
@@ -487,25 +487,22 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
             const int lp0 = 4 * G::kSize * it + 2 * G::kSize * h + 2 * gt, lp1 = lp0 + 1;
             const bool v0 = lp0 >= lo && lp0 < P, v1 = lp1 >= lo && lp1 < P;
             bool first0 = false, first1 = false, single0 = false, single1 = false;
-            int c0l = 0, c1l = 0;
             if (kWarp) {  // roles were packed next to the cell number in phase 1
                 const u32 both = *reinterpret_cast<const u16 *>(cellof + lp0);  // lp0 is even
                 const u32 b0 = v0 ? (both & 0xffu) : 0u, b1 = v1 ? (both >> 8) : 0u;
-                c0l = (int)(b0 & kCellMask);
-                c1l = (int)(b1 & kCellMask);
                 first0 = (b0 & kRoleFirst) != 0;
                 single0 = (b0 & kRoleSingle) != 0;
                 first1 = (b1 & kRoleFirst) != 0;
                 single1 = (b1 & kRoleSingle) != 0;
             } else {
                 if (v0) {
-                    c0l = cellof[lp0];
+                    const int c0l = cellof[lp0];
                     const bool even = ((lp0 - cs[c0l]) & 1) == 0, partner = lp0 + 1 < cs[c0l + 1];
                     first0 = even && partner;
                     single0 = even && !partner;
                 }
                 if (v1) {
-                    c1l = cellof[lp1];
+                    const int c1l = cellof[lp1];
                     const bool even = ((lp1 - cs[c1l]) & 1) == 0, partner = lp1 + 1 < cs[c1l + 1];
                     first1 = even && partner;
                     single1 = even && !partner;
@@ -524,7 +521,6 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
             const u32 dl = (u32)lp0 >> 1;
             has[h] = first0 || first1;
             pf[h] = first0 ? lp0 : lp1;
-            pcell[h] = first0 ? c0l : c1l;
             dflt[h] = false;
             j[h] = k[h] = 0;
             nj[h] = nk[h] = 1;

@@ -21,24 +21,23 @@ def test_migration_loopback_three_slabs():
     world = 3
     pop = global_population()
     shards = [Shard(pop, r, world) for r in range(world)]
-    for _ in range(1):
-        for s in shards:
-            s.displace()
-        packed = [s.migrator.pack() for s in shards]
-        for dst, s in enumerate(shards):
-            parts = []
-            for src in range(world):
-                records, counts = packed[src]
-                begin = sum(counts[:dst])
-                parts.append(records[begin:begin + counts[dst]])
-            s.migrator.unpack(torch.cat(parts))
-        origin, pos = moved(pop)
-        total = sum(s.check(pop) for s in shards)
-        assert total == pop["multiplicity"].size
-        assert sum(s.migrator.n_sent for s in shards) == sum(s.migrator.n_received for s in shards) > 0
-        sizes = np.concatenate([sort_and_count(s) for s in shards])
-        want = np.bincount(origin[0] * 6 + origin[1], minlength=66)
-        np.testing.assert_array_equal(sizes, want)
+    for s in shards:
+        s.displace()
+    packed = [s.migrator.pack() for s in shards]
+    for dst, s in enumerate(shards):  # what all_to_all_single delivers to rank `dst`
+        parts = []
+        for src in range(world):
+            records, counts = packed[src]
+            begin = sum(counts[:dst])
+            parts.append(records[begin:begin + counts[dst]])
+        s.migrator.unpack(torch.cat(parts))
+    origin, _ = moved(pop)
+    total = sum(s.check(pop) for s in shards)
+    assert total == pop["multiplicity"].size
+    assert sum(s.migrator.n_sent for s in shards) == sum(s.migrator.n_received for s in shards) > 0
+    sizes = np.concatenate([sort_and_count(s) for s in shards])
+    want = np.bincount(origin[0] * 6 + origin[1], minlength=66)
+    np.testing.assert_array_equal(sizes, want)
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (NCCL all-to-all)")

@@ -198,6 +198,8 @@ class ClockSampler(threading.Thread):
         self.index, self.samples, self.stop_flag = index, [], threading.Event()
 
     def run(self):
+        if self._run_nvml():
+            return
         while not self.stop_flag.is_set():
             try:
                 out = subprocess.run(
@@ -207,6 +209,34 @@ class ClockSampler(threading.Thread):
             except Exception:  # pylint: disable=broad-except
                 pass
             self.stop_flag.wait(0.1)
+
+    def _run_nvml(self):
+        """NVML directly (a query takes ~0.1 ms, so a 25 ms timed region still yields a dozen
+        samples; an nvidia-smi process takes longer than that to start); False = unavailable"""
+        try:
+            import pynvml  # pylint: disable=import-outside-toplevel
+
+            pynvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            index = int(visible.split(",")[self.index]) if visible else self.index
+            handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(handle, pynvml.NVML_CLOCK_SM)
+            bits = (("hw_slowdown", pynvml.nvmlClocksEventReasonHwSlowdown),
+                    ("hw_thermal_slowdown", pynvml.nvmlClocksEventReasonHwThermalSlowdown),
+                    ("sw_thermal_slowdown", pynvml.nvmlClocksEventReasonSwThermalSlowdown),
+                    ("sw_power_cap", pynvml.nvmlClocksEventReasonSwPowerCap))
+        except Exception:  # pylint: disable=broad-except
+            return False
+        while not self.stop_flag.is_set():
+            try:
+                mhz = pynvml.nvmlDeviceGetClockInfo(handle, pynvml.NVML_CLOCK_SM)
+                mask = pynvml.nvmlDeviceGetCurrentClocksEventReasons(handle)
+                self.samples.append([str(mhz), str(max_mhz)] +
+                                    ["Active" if mask & bit else "Not Active" for _, bit in bits])
+            except Exception:  # pylint: disable=broad-except
+                pass
+            self.stop_flag.wait(0.002)
+        return True
 
     def summary(self):
         self.stop_flag.set()

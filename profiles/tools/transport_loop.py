@@ -31,7 +31,7 @@ sys.path.insert(0, ROOT)
 from pysdm_b200 import methods as m  # noqa: E402
 from pysdm_b200.collision import DeviceCollision, Golovin  # noqa: E402
 from pysdm_b200.migration import SlabMigrator  # noqa: E402
-from pysdm_b200.sharding import cell_range  # noqa: E402
+from pysdm_b200.sharding import cell_range, reduce_products  # noqa: E402
 from pysdm_b200.storage import Storage, StorageSignature  # noqa: E402
 
 
@@ -99,7 +99,7 @@ def main():  # pylint: disable=too-many-locals,too-many-statements
         n = sim.multiplicity[idx]
         t = torch.stack([n.sum().double(), (n.double() * sim.attributes[0][idx]).sum(),
                          torch.tensor(float(sim.length), device=dev, dtype=torch.float64)])
-        dist.all_reduce(t)
+        reduce_products(sums=t)  # NCCL all-reduce of the domain-wide products
         return t.cpu().numpy()
 
     def step():

@@ -2,7 +2,8 @@
 one cell, so contiguous ranges of cells go to ranks and the collision step needs no
 communication.  Host-side logic only (pure Python/numpy): which cells and which
 super-droplets a rank owns, and how per-cell results are put back together.
-`torch.distributed` appears only in `gather_per_cell` (products / diagnostics)."""
+`torch.distributed` appears only in `gather_per_cell` and `reduce_products` (products /
+diagnostics)."""
 
 import numpy as np
 
@@ -52,3 +53,19 @@ def gather_per_cell(local_values, n_cell, group=None):
     out = [torch.empty_like(buf) for _ in range(world)]
     dist.all_gather(out, buf, group=group)
     return torch.cat([o[:n] for o, n in zip(out, sizes)])
+
+
+def reduce_products(sums=None, minima=None, maxima=None, group=None):
+    """domain-wide products of a sharded run (SURVEY.md 8e ii): every rank passes the values of
+    its own cells and gets the global ones -- `sums` (rate totals, moments over the domain,
+    super-droplet counts), `minima` (`stats_dt_min`, `healthy`: one unhealthy rank makes the
+    run unhealthy), `maxima` (`stats_n_substep`).  Each argument: a torch tensor or None; one
+    all-reduce per argument (CPU tensors with gloo, CUDA tensors with NCCL), in place.
+    Returns the tuple (sums, minima, maxima)."""
+    import torch.distributed as dist  # pylint: disable=import-outside-toplevel
+
+    for tensor, op in ((sums, dist.ReduceOp.SUM), (minima, dist.ReduceOp.MIN),
+                       (maxima, dist.ReduceOp.MAX)):
+        if tensor is not None and tensor.numel():
+            dist.all_reduce(tensor, op=op, group=group)
+    return sums, minima, maxima

@@ -68,6 +68,14 @@ def _worker(rank, world, port, n_cell, out_dir):
         t = torch.tensor([float(rank + 1)], dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         assert t.item() == world
+        # products of the whole domain: rate totals, dt_min / healthy, substep count
+        sums, minima, maxima = sharding.reduce_products(
+            sums=torch.tensor([float(e - b), 2.5 * (rank + 1)], dtype=torch.float64),
+            minima=torch.tensor([10.0 / (rank + 1), float(rank != 1)], dtype=torch.float64),
+            maxima=torch.tensor([3 + rank], dtype=torch.int64))
+        assert sums.tolist() == [float(n_cell), 2.5 * world * (world + 1) / 2]
+        assert minima.tolist() == [10.0 / world, 0.0] and maxima.tolist() == [2 + world]
+        assert sharding.reduce_products() == (None, None, None)
         with open(os.path.join(out_dir, f"ok{rank}"), "w", encoding="utf-8") as f:
             f.write("ok")
     finally:

@@ -360,6 +360,21 @@ int pysdm_b200_flag_out_of_column(const int64_t *cell_origin_z, const double *po
                                   int64_t *idx, int64_t length, int64_t idx_len,
                                   int64_t *healthy, double domain_top_level_index, void *stream);
 
+/* ---- particle injection ------------------------------------------------------------------
+ * seeding, backends/impl_numba/methods/seeding_methods.py:12-65 (caller particulator.py:447-490,
+ * dynamic dynamics/seeding.py:91-117): in physical order, every slot with multiplicity 0 --
+ * until n_inject slots have been filled -- gets idx[i] = -1 and the multiplicity and the n_attr
+ * extensive attributes ([n_attr, n_sd] / [n_attr, n_seeds] row-major) of seed
+ * seeded_particle_index[k], k = 0, 1, ... counting filled slots.  *host_n_injected = number
+ * filled (the reference asserts it equals n_inject); the stream is synchronised. */
+size_t pysdm_b200_seeding_workspace_bytes(int64_t n_sd);
+int pysdm_b200_seeding(int64_t *idx, int64_t *multiplicity, double *extensive_attributes,
+                       int64_t n_attr, int64_t n_sd, const int64_t *seeded_particle_index,
+                       const int64_t *seeded_particle_multiplicity,
+                       const double *seeded_particle_extensive_attributes, int64_t n_seeds,
+                       int64_t n_inject, int64_t *host_n_injected, void *ws, size_t ws_bytes,
+                       void *stream);
+
 /* ---- migration between the slabs of a multi-GPU run (no reference counterpart: PySDM is
  * single-process; data model of PySDM/impl/particle_attributes.py) ---------------------------
  * The first grid dimension is split into `world` balanced contiguous slabs.  A record is

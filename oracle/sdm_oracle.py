@@ -355,3 +355,18 @@ def update_position(cell_origin, position_in_cell, displacement, floor_of_positi
     lib().oracle_update_position(_p(cell_origin), _p(position_in_cell), _p(displacement),
                                  _p(floor_of_position), _p(grid), i64(n_dims), i64(n_sd),
                                  ctypes.c_int(int(apply_boundary)))
+
+
+def seeding(idx, multiplicity, extensive_attributes, seeded_particle_index,
+            seeded_particle_multiplicity, seeded_particle_extensive_attributes,
+            number_of_super_particles_to_inject):
+    """seeding_methods.py:12-65; raises like the reference's assert when fewer than the
+    requested number of empty slots exist"""
+    n_attr, n_sd = extensive_attributes.shape
+    lib().oracle_seeding.restype = i64
+    done = lib().oracle_seeding(
+        _p(idx), _p(multiplicity), _p(extensive_attributes), i64(n_attr), i64(n_sd),
+        _p(seeded_particle_index), _p(seeded_particle_multiplicity),
+        _p(seeded_particle_extensive_attributes), i64(len(seeded_particle_multiplicity)),
+        i64(number_of_super_particles_to_inject))
+    assert done == number_of_super_particles_to_inject

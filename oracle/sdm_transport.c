@@ -158,3 +158,28 @@ ORACLE_API void oracle_update_position(i64 *cell_origin, double *position_in_cel
         }
     }
 }
+
+/* seeding (particle injection), impl_numba/methods/seeding_methods.py:12-44: scan ALL slots
+ * in physical order; every slot with multiplicity 0, until n_inject have been filled, gets
+ * idx[i] = -1, the multiplicity and the A extensive attributes of seed
+ * seeded_particle_index[k] (k = 0, 1, ... in order of filling).  Returns the number injected
+ * (the reference asserts it equals n_inject). */
+ORACLE_API i64 oracle_seeding(i64 *idx, i64 *multiplicity, double *extensive_attributes,
+                              i64 n_attr, i64 n_sd, const i64 *seeded_particle_index,
+                              const i64 *seeded_particle_multiplicity,
+                              const double *seeded_particle_extensive_attributes, i64 n_seeds,
+                              i64 n_inject)
+{
+    i64 done = 0;
+    for (i64 i = 0; i < n_sd; ++i) {
+        if (done == n_inject) break;
+        if (multiplicity[i] == 0) {
+            idx[i] = -1;
+            const i64 s = seeded_particle_index[done++];
+            multiplicity[i] = seeded_particle_multiplicity[s];
+            for (i64 a = 0; a < n_attr; ++a)
+                extensive_attributes[a * n_sd + i] = seeded_particle_extensive_attributes[a * n_seeds + s];
+        }
+    }
+    return done;
+}

@@ -78,6 +78,8 @@ SIGNATURES = {
     "pysdm_b200_calculate_displacement": (INT, (INT, INT, INT, P, P, P, P, P, I64, F64, P)),
     "pysdm_b200_flag_precipitated": (INT, (P, P, P, P, P, I64, I64, P, F64, P, P, P)),
     "pysdm_b200_flag_out_of_column": (INT, (P, P, P, I64, I64, P, F64, P)),
+    "pysdm_b200_seeding_workspace_bytes": (SIZE, (I64,)),
+    "pysdm_b200_seeding": (INT, (P, P, P, I64, I64, P, P, P, I64, I64, P, P, SIZE, P)),
     "pysdm_b200_migration_destination": (INT, (P, P, P, P, I64, I64, INT, P, I64, P)),
     "pysdm_b200_migration_pack": (INT, (P, I64, P, I64, I64, P, P, I64, P, P, INT, I64, P)),
     "pysdm_b200_migration_unpack": (INT, (P, I64, P, P, P, P, I64, P, P, INT, I64, P)),

@@ -327,6 +327,16 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
         m.flag_out_of_column(cell_origin.data, position_in_cell.data, idx.data, length,
                              healthy.data, domain_top_level_index)
 
+    # ---- particle injection: seeding_methods.py:46-65 -------------------------------------------
+    @staticmethod
+    def seeding(*, idx, multiplicity, extensive_attributes, seeded_particle_index,
+                seeded_particle_multiplicity, seeded_particle_extensive_attributes,
+                number_of_super_particles_to_inject: int):
+        m.seeding(idx.data, multiplicity.data, extensive_attributes.data,
+                  seeded_particle_index.data, seeded_particle_multiplicity.data,
+                  seeded_particle_extensive_attributes.data,
+                  number_of_super_particles_to_inject)
+
     # ---- physics (physics_methods.py:107-133) -----------------------------------------------
     def volume_of_water_mass(self, volume, mass):
         m.volume_of_water_mass(volume.data, mass.data, self.rho_w)
@@ -337,7 +347,7 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
 
 # everything outside the collision path: explicit NotImplementedError
 for _name in (
-        "condensation", "make_condensation_solver", "seeding", "freeze_singular",
+        "condensation", "make_condensation_solver", "freeze_singular",
         "freeze_time_dependent", "freeze_time_dependent_homogeneous", "thaw_instantaneous",
         "oxidation", "dissolution", "chem_recalculate_drop_data", "chem_recalculate_cell_data",
         "equilibrate_H", "isotopic_delta", "isotopic_fractionation", "deposition",

@@ -10,7 +10,7 @@ CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libpysdm_b200.so")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 SOURCES = ("index.cu", "pairs.cu", "storage_ops.cu", "physics.cu", "breakup.cu", "transport.cu",
-           "migration.cu", "fused.cu")
+           "migration.cu", "seeding.cu", "fused.cu")
 NVCC_FLAGS = (
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     # no implicit FMA contraction: results must match the reference's IEEE sequence;

@@ -467,3 +467,23 @@ def row_modulo_int(out, divisor):
     n_rows, n_cols = out.shape if out.dim() == 2 else (1, out.numel())
     check(_lib.load().pysdm_b200_row_modulo_i64(_pi(out), _pi(divisor), n_rows, n_cols,
                                                 _stream()), "row_modulo")
+
+
+def seeding(idx, multiplicity, extensive_attributes, seeded_particle_index,
+            seeded_particle_multiplicity, seeded_particle_extensive_attributes,
+            number_of_super_particles_to_inject):
+    """seeding_methods.py:12-65; the reference's closing assert (as many injected as asked
+    for) is raised here from the count the kernel reports"""
+    lib = _lib.load()
+    n_attr, n_sd = extensive_attributes.shape
+    n_seeds = seeded_particle_multiplicity.numel()
+    assert seeded_particle_extensive_attributes.shape == (n_attr, n_seeds)
+    ws = WS.dev("seeding", lib.pysdm_b200_seeding_workspace_bytes(int(n_sd)), idx.device)
+    box = WS.box()
+    check(lib.pysdm_b200_seeding(
+        _pi(idx), _pi(multiplicity), _pf(extensive_attributes), int(n_attr), int(n_sd),
+        _pi(seeded_particle_index), _pi(seeded_particle_multiplicity),
+        _pf(seeded_particle_extensive_attributes), int(n_seeds),
+        int(number_of_super_particles_to_inject), box.data_ptr(), _p(ws), ws.numel(), _stream()),
+        "seeding")
+    assert int(box[0]) == int(number_of_super_particles_to_inject)

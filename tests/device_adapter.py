@@ -323,3 +323,12 @@ def update_position(cell_origin, position_in_cell, displacement, floor_of_positi
     cell_origin[...] = s_origin.to_ndarray()
     position_in_cell[...] = s_pos.to_ndarray()
     floor_of_position[...] = s_tmp.to_ndarray()
+
+
+def seeding(idx, multiplicity, extensive_attributes, seeded_particle_index,
+            seeded_particle_multiplicity, seeded_particle_extensive_attributes,
+            number_of_super_particles_to_inject):
+    m = _Mirror(idx, multiplicity, extensive_attributes, seeded_particle_index,
+                seeded_particle_multiplicity, seeded_particle_extensive_attributes)
+    dev.seeding(*m.dev, number_of_super_particles_to_inject)
+    m.back(0, 1, 2)

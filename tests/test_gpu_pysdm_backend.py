@@ -321,3 +321,95 @@ def test_b200_backend_physics_cases(pysdm, case):
             events += int(dyn_b.breakup_rate.to_ndarray().sum())
         events += int(b["coalescence_rate"].sum())
     assert events > 0
+
+
+# ---- the dynamics next to the collision step that touch the same SoA state --
+def test_seeding_dynamic_with_coalescence(pysdm):
+    """`PySDM.dynamics.Seeding` (dynamics/seeding.py:91-117 -> particulator.py:447-490 ->
+    backend.seeding) next to `Coalescence` in a box padded with empty slots, after the
+    reference's own tests/unit_tests/dynamics/test_seeding.py: Numba backend vs B200 backend,
+    same uniforms; the injected slots, the shuffled seed index and the whole state are
+    bit-identical after every step."""
+    from PySDM import Builder, Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics import Coalescence, Seeding  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics.collisions.collision_kernels import Golovin  # pylint: disable=import-outside-toplevel
+    from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200  # pylint: disable=import-outside-toplevel
+
+    n_initial, n_pad, n_seeds = 600, 200, 16
+    rng = np.random.default_rng(5)
+    volume = np.pad(rng.exponential(4.0 / 3 * np.pi * (30.531e-6) ** 3, n_initial), (0, n_pad))
+    multiplicity = np.pad(rng.integers(1, 5, n_initial).astype(float), (0, n_pad),
+                          constant_values=np.nan)
+    seed_mass = list(rng.exponential(1e-9, n_seeds))
+    seed_mult = list(rng.integers(1, 9, n_seeds))
+
+    def make(backend):
+        builder = Builder(n_sd=n_initial + n_pad, backend=backend, environment=Box(dt=1.0, dv=1e-7))
+        builder.add_dynamic(Coalescence(collision_kernel=Golovin(b=1.5e3), adaptive=False))
+        builder.add_dynamic(Seeding(
+            super_droplet_injection_rate=lambda time: 3 if 2 <= time < 7 else 0,
+            seeded_particle_multiplicity=seed_mult,
+            seeded_particle_extensive_attributes={"signed water mass": seed_mass}))
+        return builder.build(attributes={"volume": volume.copy(),
+                                         "multiplicity": multiplicity.copy()}, products=())
+
+    fkw = dict(fastmath=False, seed=77)
+    ref, sut = make(CPU(Formulae(**fkw))), make(B200(Formulae(**fkw), host_rng=True))
+    counts = []
+    for step in range(10):
+        ref.run(1)
+        sut.run(1)
+        a, b = snapshot(sut), snapshot(ref)
+        n = b["length"]
+        assert a["length"] == n, f"step {step}: length"
+        np.testing.assert_array_equal(a["idx"][:n], b["idx"][:n], f"step {step}: idx")
+        np.testing.assert_array_equal(a["multiplicity"], b["multiplicity"], f"step {step}")
+        assert_same_f64(a["attributes"], b["attributes"], f"step {step}: attributes")
+        np.testing.assert_array_equal(sut.dynamics["Seeding"].index.to_ndarray(),
+                                      ref.dynamics["Seeding"].index.to_ndarray())
+        counts.append(int(ref.attributes.super_droplet_count))
+        assert int(sut.attributes.super_droplet_count) == counts[-1]
+    assert max(np.diff(counts)) > 0  # injections did happen
+    assert int(snapshot(ref)["coalescence_rate"].sum()) > 0
+
+
+@pytest.mark.parametrize("constant", (True, False))
+def test_relaxed_velocity_dynamic(pysdm, constant):
+    """`PySDM.dynamics.RelaxedVelocity` (dynamics/relaxed_velocity.py:60-90: Storage `product`,
+    `*=`, `+=`, `**=`, `exp` on the SoA state + the `relative fall momentum` / `terminal
+    velocity` attributes) on the B200 backend vs the Numba backend, after the reference's
+    tests/unit_tests/dynamics/test_relaxed_velocity.py; 1e-12 relative (CUDA pow/exp)."""
+    from PySDM import Builder, Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics import RelaxedVelocity  # pylint: disable=import-outside-toplevel
+    from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200  # pylint: disable=import-outside-toplevel
+
+    n_sd = 512
+    rng = np.random.default_rng(11)
+    attributes = {
+        "multiplicity": rng.integers(1, 100, n_sd).astype(np.int64),
+        "volume": 4 / 3 * np.pi * (rng.exponential(0.2e-3, n_sd) + 5e-6) ** 3,
+        "relative fall momentum": np.zeros(n_sd),
+    }
+
+    def make(backend):
+        builder = Builder(n_sd=n_sd, backend=backend, environment=Box(dt=1.0, dv=1.0))
+        builder.add_dynamic(RelaxedVelocity(c=2.0, constant=constant))
+        builder.request_attribute("relative fall velocity")
+        builder.request_attribute("terminal velocity")
+        return builder.build(attributes={k: v.copy() for k, v in attributes.items()}, products=())
+
+    ref, sut = make(CPU(Formulae(fastmath=False))), make(B200(Formulae(fastmath=False)))
+    for step in range(4):
+        ref.run(1)
+        sut.run(1)
+        for name in ("relative fall momentum", "relative fall velocity", "terminal velocity"):
+            expected = ref.attributes[name].to_ndarray()
+            np.testing.assert_allclose(sut.attributes[name].to_ndarray(), expected, rtol=1e-12,
+                                       atol=0, err_msg=f"step {step}: {name}")
+            assert np.abs(expected).max() > 0

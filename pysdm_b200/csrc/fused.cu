@@ -7,7 +7,9 @@
 //   shuffle_local            impl_numba/methods/index_methods.py:32-44
 //   find_pairs               impl_numba/methods/pair_methods.py:34-55
 //   sort_within_pair_by_attr pair_methods.py:126-140          (attr = multiplicity)
-//   collision kernel         collision_kernels/{golovin,constantK,linear}.py  (sum_pair, *=, +=)
+//   collision kernel         collision_kernels/{golovin,constantK,linear}.py  (sum_pair, *=, +=),
+//                            geometric.py:15-22 (sum_pair of radius, **= 2, *=, distance_pair of
+//                            the fall velocity, *=) on the per-SD radius / velocity attributes
 //   max_pair, *= kernel_temp pair_methods.py:57-75, collision.py:249-254
 //   normalize                impl_numba/methods/collisions_methods.py:633-662 (incl. quirk A1)
 //   prob /= substeps         collision.py:279
@@ -39,7 +41,7 @@
 // C-ABI argument block: include/pysdm_b200.h (mirrored by ctypes in pysdm_b200/_lib.py)
 typedef pysdm_b200_fused_args FusedArgs;
 
-enum { KERNEL_GOLOVIN = 0, KERNEL_CONSTANT_K = 1, KERNEL_LINEAR = 2 };
+enum { KERNEL_GOLOVIN = 0, KERNEL_CONSTANT_K = 1, KERNEL_LINEAR = 2, KERNEL_GEOMETRIC = 3 };
 
 #ifndef PYSDM_WARP_POS
 #define PYSDM_WARP_POS 1024
@@ -104,6 +106,20 @@ __device__ __forceinline__ double kernel_temp_of(double vsum, double a, double b
     if (K == KERNEL_GOLOVIN) return vsum * b;   // golovin.py:14-16
     if (K == KERNEL_CONSTANT_K) return a;       // constantK.py: output.fill(a)
     return vsum * b + a;                        // linear.py: sum; *= b; += a  (no FMA: -fmad=false)
+}
+
+// Geometric (collision_kernels/geometric.py:15-22): output = r_j + r_k (sum_pair); output **= 2
+// (Storage.__ipow__ = sign(x) |x|^e, impl_numba/storage_impl.py power; csrc/storage_ops.cu
+// signed_pow); output *= PI * collection_efficiency (= a, multiplied on the host as the
+// reference does); pair_tmp = |u_j - u_k| (distance_pair); output *= pair_tmp
+__device__ __forceinline__ double geometric_kernel_temp(double r_j, double r_k, double u_j,
+                                                        double u_k, double a)
+{
+    const double x = r_j + r_k;
+    const double sgn = x > 0 ? 1.0 : (x < 0 ? -1.0 : (x == 0 ? 0.0 : x));
+    double out = sgn * (fabs(x) * fabs(x));
+    out = out * a;
+    return out * fabs(u_j - u_k);
 }
 
 // ---- pre-pass: norm_factor per cell rank (normalize, collisions_methods.py:639-646) ---------
@@ -270,7 +286,9 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     }
     const i64 n_pairs_active = a.length / 2;
     // literal chain for a slot without a pair: max_pair -> 0; *= kernel_temp; normalize
-    const double prob_nopair = 0.0 * kernel_temp_of<K>(0.0, a.kernel_a, a.kernel_b);
+    const double prob_nopair =
+        0.0 * (K == KERNEL_GEOMETRIC ? geometric_kernel_temp(0.0, 0.0, 0.0, 0.0, a.kernel_a)
+                                     : kernel_temp_of<K>(0.0, a.kernel_a, a.kernel_b));
     const bool unit_substeps = a.substeps == 1.0;
     const double rho_rcp = 1.0 / a.rho_w;
     const bool rho_ok = a.reserved != 0;  // host-checked precondition of div_by
@@ -462,7 +480,8 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     }
 
     // ---- phase 4: two pair slots per thread and iteration ---------------------------------
-    const double *mass = a.attributes + a.mass_row * a.n_sd;
+    // per-SD operand of the collision kernel: water mass, or the radius attribute (Geometric)
+    const double *mass = K == KERNEL_GEOMETRIC ? a.radius : a.attributes + a.mass_row * a.n_sd;
     const bool flag_al = (((uintptr_t)a.is_first_in_pair) & 1) == 0;
     const bool vec_out = (((uintptr_t)a.idx_out) & 15) == 0;
     // batch-local bases (32-bit offsets in the loop); dl = local pair slot = lp0 / 2
@@ -482,6 +501,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
         u32 j[2], k[2];
         i64 nj[2], nk[2];
         double mj[2], mk[2], nf[2];
+        double uj[2] = {0.0, 0.0}, uk[2] = {0.0, 0.0};  // fall velocities (Geometric)
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int lp0 = 4 * G::kSize * it + 2 * G::kSize * h + 2 * gt, lp1 = lp0 + 1;
@@ -559,6 +579,10 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
                     mj[h] = mass[j[h]];
                     mk[h] = mass[k[h]];
                 }
+                if (K == KERNEL_GEOMETRIC) {
+                    uj[h] = a.fall_velocity[j[h]];
+                    uk[h] = a.fall_velocity[k[h]];
+                }
             }
 
         // uniforms of this warp's 2 x 32 slots: 32 Philox blocks, one per lane (block b holds
@@ -605,10 +629,16 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
                     out_b[(u32)pf[h] + 1] = (i64)sk;
                 }
                 // volume = mass / rho_w (physics_methods.py:107-119); sum_pair; kernel; max_pair
-                double vsum = 0.0;
-                if (K != KERNEL_CONSTANT_K)
-                    vsum = div_by(m_j, a.rho_w, rho_rcp, rho_ok) + div_by(m_k, a.rho_w, rho_rcp, rho_ok);
-                double prob = i64_to_f64(n_j) * kernel_temp_of<K>(vsum, a.kernel_a, a.kernel_b);
+                double kernel_temp;
+                if (K == KERNEL_GEOMETRIC) {  // |u_j - u_k| is symmetric: no need to swap uj / uk
+                    kernel_temp = geometric_kernel_temp(m_j, m_k, uj[h], uk[h], a.kernel_a);
+                } else {
+                    double vsum = 0.0;
+                    if (K != KERNEL_CONSTANT_K)
+                        vsum = div_by(m_j, a.rho_w, rho_rcp, rho_ok) + div_by(m_k, a.rho_w, rho_rcp, rho_ok);
+                    kernel_temp = kernel_temp_of<K>(vsum, a.kernel_a, a.kernel_b);
+                }
+                double prob = i64_to_f64(n_j) * kernel_temp;
                 prob = prob * nf[h];
                 if (!unit_substeps) prob = prob / a.substeps;
                 g_raw = ceil_exact(prob - rnd[h]);
@@ -726,6 +756,9 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
     case KERNEL_CONSTANT_K:
         return dispatch_fused<KERNEL_CONSTANT_K>(a, n_batches, philox, warp, aggregate, st);
     case KERNEL_LINEAR: return dispatch_fused<KERNEL_LINEAR>(a, n_batches, philox, warp, aggregate, st);
+    case KERNEL_GEOMETRIC:
+        if (a.radius == nullptr || a.fall_velocity == nullptr) return (int)cudaErrorInvalidValue;
+        return dispatch_fused<KERNEL_GEOMETRIC>(a, n_batches, philox, warp, aggregate, st);
     default: return (int)cudaErrorInvalidValue;
     }
 }

@@ -10,7 +10,8 @@ fused kernel (csrc/fused.cu) -- for users of the unchanged PySDM orchestration
 It derives from the reference's own class (PySDM/dynamics/collisions/collision.py:46-290,
 `Coalescence` :293-330), registers under the same name ("Collision"), allocates the same
 storages, and overrides `step()` only: when the configuration is one the fused kernel
-covers -- B200 backend, non-adaptive, "local" croupier, Golovin / ConstantK / Linear kernel,
+covers -- B200 backend, non-adaptive, "local" croupier, Golovin / ConstantK / Linear /
+Geometric kernel,
 no breakup, every cell within the fused kernel's size limit, `optimized_random` off -- one
 launch replaces the sequence `Collision.step` issues (:196-234) and writes every storage
 that sequence writes (idx, pair flags, gamma, multiplicities, attributes, norm factors, rate
@@ -23,8 +24,15 @@ import torch
 from . import methods as m
 from .random import Random
 
+def _geometric(k):
+    """collision_kernels/geometric.py:18: the factor `output *= const.PI * collection_efficiency`"""
+    from PySDM.physics import constants as const  # pylint: disable=import-outside-toplevel
+
+    return (const.PI * k.collection_efficiency, 0.0)
+
+
 _KERNELS = {"Golovin": lambda k: (0.0, k.b), "ConstantK": lambda k: (k.a, 0.0),
-            "Linear": lambda k: (k.a, k.b)}
+            "Linear": lambda k: (k.a, k.b), "Geometric": _geometric}
 
 
 def make_fused_coalescence():
@@ -87,6 +95,12 @@ def make_fused_coalescence():
             else:  # injected uniforms (parity runs with the Numba backend's stream)
                 pairs_rand, rand = self.rnd_opt_coll.get_random_arrays()
                 kw = {"u01": pairs_rand.data, "rand": rand.data}
+            if name == "Geometric":
+                # dependent attributes, recomputed by the orchestration when the water mass was
+                # marked updated (attributes/physics/radius.py:15-17, relative_fall_velocity.py,
+                # terminal_velocity.py) -- the operands geometric.py:15-22 gathers
+                kw["radius"] = attrs["radius"].data
+                kw["fall_velocity"] = attrs["relative fall velocity"].data
             length = len(idx)
             ext = attrs.get_extensive_attribute_storage()
             substeps = self._Collision__substeps  # pylint: disable=no-member

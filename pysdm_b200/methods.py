@@ -258,9 +258,12 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
                          collision_rate_deficit, coalescence_rate, healthy, status, length,
                          max_cell, kernel, kernel_a=0.0, kernel_b=0.0, timestep, dv, rho_w,
                          substeps=1, mass_row=0, u01=None, rand=None, seed=0, call_u01=0,
-                         call_rand=0, nf_slot, refresh_nf=True, gate=None, epoch=1):
+                         call_rand=0, nf_slot, refresh_nf=True, gate=None, epoch=1, radius=None,
+                         fall_velocity=None):
     """one Collision.step() in one launch; returns the CUDA error code (9 = a cell is
-    larger than the fused path supports -> use the method-level functions)"""
+    larger than the fused path supports -> use the method-level functions).  kernel
+    "Geometric": kernel_a = PI * collection_efficiency, `radius` and `fall_velocity` = the
+    per-SD attributes of that name (f64[n_sd])"""
     n_attr, n_sd = attributes.shape
     args = _lib.FusedArgs(
         idx_in=_pi(idx_in), idx_out=_pi(idx_out), cell_start=_pi(cell_start),
@@ -275,7 +278,7 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         dv=float(dv), rho_w=float(rho_w), substeps=float(substeps), kernel_a=float(kernel_a),
         kernel_b=float(kernel_b), kernel=_lib.KERNELS[kernel], reserved=0,
         max_cell_size=int(max_cell), nf_slot=_pf(nf_slot), refresh_nf=int(bool(refresh_nf)),
-        gate=_pi(gate), epoch=int(epoch))
+        gate=_pi(gate), epoch=int(epoch), radius=_pf(radius), fall_velocity=_pf(fall_velocity))
     return _lib.load().pysdm_b200_fused_collision_step(ctypes.byref(args), _stream())
 
 

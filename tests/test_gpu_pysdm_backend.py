@@ -347,7 +347,7 @@ def test_seeding_dynamic_with_coalescence(pysdm):
     seed_mult = list(rng.integers(1, 9, n_seeds))
 
     def make(backend):
-        builder = Builder(n_sd=n_initial + n_pad, backend=backend, environment=Box(dt=1.0, dv=1e-7))
+        builder = Builder(n_sd=n_initial + n_pad, backend=backend, environment=Box(dt=1.0, dv=1e-5))
         builder.add_dynamic(Coalescence(collision_kernel=Golovin(b=1.5e3), adaptive=False))
         builder.add_dynamic(Seeding(
             super_droplet_injection_rate=lambda time: 3 if 2 <= time < 7 else 0,
@@ -413,3 +413,63 @@ def test_relaxed_velocity_dynamic(pysdm, constant):
             np.testing.assert_allclose(sut.attributes[name].to_ndarray(), expected, rtol=1e-12,
                                        atol=0, err_msg=f"step {step}: {name}")
             assert np.abs(expected).max() > 0
+
+
+@pytest.mark.parametrize("host_rng", (True, False))
+@pytest.mark.parametrize("grid", ((1,), (4, 5)))
+def test_fused_coalescence_geometric(pysdm, grid, host_rng):
+    """`FusedCoalescence` with the Geometric (gravitational) kernel, collision_kernels/
+    geometric.py:15-22: the fused kernel gathers the orchestration's own "radius" and "relative
+    fall velocity" attributes.  host_rng=False: against the stock dynamic on the B200 backend,
+    same device Philox stream -- everything bit-identical.  host_rng=True: against the Numba
+    backend with the same uniforms -- integers / permutation / gamma identical, attributes to
+    1e-12 (radius goes through CUDA's pow there, glibc's here)."""
+    from PySDM import Builder, Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics.collisions.collision_kernels import Geometric  # pylint: disable=import-outside-toplevel
+    from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
+    from PySDM.impl.mesh import Mesh  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200, FusedCoalescence  # pylint: disable=import-outside-toplevel
+
+    n_sd, n_cell = 2048, int(np.prod(grid))
+    rng = np.random.default_rng(17)
+    attributes = {
+        "multiplicity": rng.integers(200, 4000, n_sd).astype(np.int64),
+        "volume": 4 / 3 * np.pi * (rng.exponential(12e-6, n_sd) + 2e-6) ** 3,
+    }
+    if n_cell > 1:
+        attributes["cell id"] = rng.integers(0, n_cell, n_sd).astype(np.int64)
+
+    def make(backend, dynamic):
+        env = Box(dv=0.05 / n_cell, dt=10.0)
+        if n_cell > 1:
+            env.mesh = Mesh(grid, size=grid, dv=0.05 / n_cell)
+        builder = Builder(n_sd=n_sd, backend=backend, environment=env)
+        builder.add_dynamic(dynamic(collision_kernel=Geometric(collection_efficiency=0.9),
+                                    adaptive=False, croupier="local"))
+        return builder.build(attributes={k: v.copy() for k, v in attributes.items()}, products=())
+
+    fkw = dict(fastmath=False, seed=31)
+    ref = make(CPU(Formulae(**fkw)) if host_rng else B200(Formulae(**fkw)), Coalescence)
+    sut = make(B200(Formulae(**fkw), host_rng=host_rng), FusedCoalescence)
+    for step in range(6):
+        ref.run(1)
+        sut.run(1)
+        a, b = snapshot(sut), snapshot(ref)
+        n = b["length"]
+        assert a["length"] == n, f"step {step}: length"
+        np.testing.assert_array_equal(a["idx"][:n], b["idx"][:n], f"step {step}: idx")
+        np.testing.assert_array_equal(a["flag"][:n], b["flag"][:n], f"step {step}: flag")
+        flips = int((a["gamma"] != b["gamma"]).sum())
+        assert flips == 0, f"step {step}: {flips} gamma values differ"
+        np.testing.assert_array_equal(a["multiplicity"], b["multiplicity"], f"step {step}")
+        if host_rng:
+            np.testing.assert_allclose(a["attributes"], b["attributes"], rtol=1e-12, atol=0)
+        else:
+            assert_same_f64(a["attributes"], b["attributes"], f"step {step}: attributes")
+        for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate"):
+            np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
+    assert sut.dynamics["Collision"].n_fused_steps == 6
+    assert int(snapshot(ref)["coalescence_rate"].sum()) > 0

@@ -41,6 +41,8 @@ def dynamics(config, fused=False):
         return Coalescence(collision_kernel=Golovin(b=1.5e3), adaptive=False)
     if config == 4:  # bench.py's workload (configs[4]) through the PySDM orchestration
         return Coalescence(collision_kernel=Golovin(b=1.5e3), adaptive=False, croupier="local")
+    if config == 5:  # the same multi-cell population with the gravitational (Geometric) kernel
+        return Coalescence(collision_kernel=Geometric(), adaptive=False, croupier="local")
     if config == 1:  # Berry 1967 box
         return Coalescence(collision_kernel=Hydrodynamic(), adaptive=True,
                            dt_coal_range=(0.1, 100.0))
@@ -66,6 +68,9 @@ SETUP = {
     3: dict(name="Sc-rain collision step, Geometric + adaptive, 2^22 SDs in 32768 cells", log2=22,
             dt=5.0, dv=(1500 / 512) ** 2, r0=10e-6, norm=None, fkw={}, sd_per_cell=128),
     4: dict(name="Golovin multi-cell coalescence, 2^24 SDs in 2^17 cells (bench.py workload)",
+            log2=24, dt=1.0, dv=1.0, r0=30.531e-6, norm=None, fkw={}, sd_per_cell=128,
+            multiplicity=2 ** 20),
+    5: dict(name="Geometric multi-cell coalescence, non-adaptive, 2^24 SDs in 2^17 cells",
             log2=24, dt=1.0, dv=1.0, r0=30.531e-6, norm=None, fkw={}, sd_per_cell=128,
             multiplicity=2 ** 20),
 }

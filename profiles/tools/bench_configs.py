@@ -125,6 +125,8 @@ def run(config, backend_name, steps, log2=None):
     sync()
     dt = time.perf_counter() - t0
     dyn = particulator.dynamics["Collision"]
+    if backend_name == "B200F" and KERNEL_ONLY:
+        kernel_only(particulator, c, n_sd)
     substeps = float(np.mean(dyn.stats_n_substep.to_ndarray())) if config else float(steps + 2)
     print(json.dumps({
         "config": c["name"], "backend": backend_name, "n_sd": n_sd, "steps": steps,
@@ -134,6 +136,55 @@ def run(config, backend_name, steps, log2=None):
         "super_droplets_left": int(particulator.attributes.super_droplet_count)}), flush=True)
 
 
+KERNEL_ONLY = False
+
+
+def kernel_only(particulator, c, n_sd, launches=50):
+    """the fused launch alone (no orchestration, no dependent-attribute refresh between
+    launches: same memory traffic, radius / velocity simply not updated), CUDA events on the
+    launch stream; roofline by the algorithmic bytes of DESIGN.md 3.2 (+16 B/SD for the two
+    gathered attributes of the Geometric kernel)"""
+    import torch
+
+    from pysdm_b200 import methods as m
+
+    dyn = particulator.dynamics["Collision"]
+    calls = []
+    real = m.fused_collision_step
+
+    def spy(**kw):
+        calls.append(kw)
+        return real(**kw)
+
+    m.fused_collision_step = spy
+    try:
+        particulator.run(1)
+    finally:
+        m.fused_collision_step = real
+    kw = dict(calls[-1])
+    a, b = kw["idx_in"], kw["idx_out"]
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    for i in range(launches + 5):
+        if i == 5:
+            ev[0].record()
+        kw["idx_in"], kw["idx_out"] = (a, b) if i % 2 == 0 else (b, a)
+        kw["call_u01"], kw["call_rand"] = 1000 + 2 * i, 1001 + 2 * i
+        kw["refresh_nf"] = False
+        assert real(**kw) == 0
+    ev[1].record()
+    torch.cuda.synchronize()
+    ms = ev[0].elapsed_time(ev[1]) / launches
+    geometric = kw["kernel"] == "Geometric"
+    bytes_per_sd = 57 + 16 * kw["attributes"].shape[0] + (16 if geometric else 0)
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+    gbs = bytes_per_sd * n_sd / ms / 1e6
+    print(json.dumps({"config": c["name"], "what": "fused launch only (CUDA events)",
+                      "kernel": kw["kernel"], "launches": launches, "kernel_ms": ms,
+                      "algorithmic_bytes_per_sd": bytes_per_sd, "achieved_gbs": gbs,
+                      "peak_gbs_measured": peak, "frac": gbs / peak}), flush=True)
+    assert dyn.n_fused_steps > 0
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=10)
@@ -141,7 +192,10 @@ if __name__ == "__main__":
     ap.add_argument("--configs", default="0,1,2")
     ap.add_argument("--backends", default="B200,CPU")
     ap.add_argument("--log2", type=int, default=None)
+    ap.add_argument("--kernel-only", action="store_true",
+                    help="B200F: also time the fused launch alone with CUDA events")
     a = ap.parse_args()
+    KERNEL_ONLY = a.kernel_only
     for cfg in (int(x) for x in a.configs.split(",")):
         for be in a.backends.split(","):
             run(cfg, be, a.steps if be.startswith("B200") else a.cpu_steps, a.log2)

@@ -96,8 +96,19 @@ __global__ void k_interpolation(double *__restrict__ output, const double *__res
         return;
     }
     double fr = factor * r;
-    i64 r_id = (i64)fr;
-    double r_rest = fmod(fr, 1.0) / factor;
+    i64 r_id;
+    double frac;  // (factor * r) % 1
+    if (fr >= 0.0 && fr < 2251799813685248.0) {  // NaN takes the other branch
+        // exact, without the 64-bit conversion and the fmod loop: 2^52 + floor(fr) by a
+        // round-down add, the integer from its mantissa, fr - floor(fr) = fmod(fr, 1) exactly
+        const double t = __dadd_rd(fr, 4503599627370496.0);
+        r_id = (i64)((u64)__double_as_longlong(t) & 0x000FFFFFFFFFFFFFull);
+        frac = fr - (t - 4503599627370496.0);
+    } else {
+        r_id = (i64)fr;
+        frac = fmod(fr, 1.0);
+    }
+    double r_rest = frac / factor;
     output[i] = b[r_id] + r_rest * c[r_id];
 }
 

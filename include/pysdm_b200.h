@@ -191,9 +191,11 @@ typedef struct pysdm_b200_fused_args {
     uint64_t seed, call_u01, call_rand; /* Philox stream: Random(seed), call numbers */
     double timestep, dv, rho_w, substeps;
     double kernel_a, kernel_b;  /* Golovin: b; ConstantK: a; Linear: a, b;
-                                   Geometric: a = PI * collection_efficiency */
-    int32_t kernel;             /* 0 Golovin, 1 ConstantK, 2 Linear, 3 Geometric (geometric.py:15-22:
-                                   gathers `radius` and `fall_velocity` instead of the water mass) */
+                                   Geometric: a = PI * collection_efficiency;
+                                   Hydrodynamic: a = PI */
+    int32_t kernel;             /* 0 Golovin, 1 ConstantK, 2 Linear, 3 Geometric (geometric.py:15-22),
+                                   4 Hydrodynamic / Parameterized (impl/parameterized.py:13-30); 3 and 4
+                                   gather `radius` and `fall_velocity` instead of the water mass */
     int32_t reserved;
     int64_t max_cell_size;      /* upper bound of cell_start[c+1]-cell_start[c] (host hint) */
     double *nf_slot;            /* [n_sd / 2] scratch: norm_factor[cell_idx[cell_id[d]]] per pair
@@ -210,8 +212,11 @@ typedef struct pysdm_b200_fused_args {
     int64_t epoch;              /* != 0, different for consecutive launches */
     uint32_t philox_round_keys[20]; /* filled in by the launcher from `seed` */
     int64_t shuffle_only;       /* set by pysdm_b200_shuffle_local_batched: stop after the shuffle */
-    const double *radius;        /* [n_sd] kernel 3 only: the "radius" attribute */
-    const double *fall_velocity; /* [n_sd] kernel 3 only: the "relative fall velocity" attribute */
+    const double *radius;        /* [n_sd] kernels 3, 4: the "radius" attribute */
+    const double *fall_velocity; /* [n_sd] kernels 3, 4: the "relative fall velocity" attribute */
+    double berry_params[13];     /* kernel 4: (A, B, D1, D2, E1, E2, F1, F2, G1, G2, G3, Mf, Mg) as */
+    int64_t berry_int_mask;      /* in pysdm_b200_linear_collection_efficiency */
+    double berry_unit;
 } pysdm_b200_fused_args;
 
 int64_t pysdm_b200_fused_max_cell_size(void);

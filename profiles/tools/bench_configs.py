@@ -43,6 +43,8 @@ def dynamics(config, fused=False):
         return Coalescence(collision_kernel=Golovin(b=1.5e3), adaptive=False, croupier="local")
     if config == 5:  # the same multi-cell population with the gravitational (Geometric) kernel
         return Coalescence(collision_kernel=Geometric(), adaptive=False, croupier="local")
+    if config == 6:  # ... and with Berry's hydrodynamic collection efficiency
+        return Coalescence(collision_kernel=Hydrodynamic(), adaptive=False, croupier="local")
     if config == 1:  # Berry 1967 box
         return Coalescence(collision_kernel=Hydrodynamic(), adaptive=True,
                            dt_coal_range=(0.1, 100.0))
@@ -68,6 +70,9 @@ SETUP = {
     3: dict(name="Sc-rain collision step, Geometric + adaptive, 2^22 SDs in 32768 cells", log2=22,
             dt=5.0, dv=(1500 / 512) ** 2, r0=10e-6, norm=None, fkw={}, sd_per_cell=128),
     4: dict(name="Golovin multi-cell coalescence, 2^24 SDs in 2^17 cells (bench.py workload)",
+            log2=24, dt=1.0, dv=1.0, r0=30.531e-6, norm=None, fkw={}, sd_per_cell=128,
+            multiplicity=2 ** 20),
+    6: dict(name="Hydrodynamic multi-cell coalescence, non-adaptive, 2^24 SDs in 2^17 cells",
             log2=24, dt=1.0, dv=1.0, r0=30.531e-6, norm=None, fkw={}, sd_per_cell=128,
             multiplicity=2 ** 20),
     5: dict(name="Geometric multi-cell coalescence, non-adaptive, 2^24 SDs in 2^17 cells",
@@ -174,7 +179,7 @@ def kernel_only(particulator, c, n_sd, launches=50):
     ev[1].record()
     torch.cuda.synchronize()
     ms = ev[0].elapsed_time(ev[1]) / launches
-    geometric = kw["kernel"] == "Geometric"
+    geometric = kw["kernel"] in ("Geometric", "Hydrodynamic")
     bytes_per_sd = 57 + 16 * kw["attributes"].shape[0] + (16 if geometric else 0)
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     gbs = bytes_per_sd * n_sd / ms / 1e6

@@ -102,10 +102,11 @@ class FusedArgs(ctypes.Structure):
         + [("kernel", ctypes.c_int32), ("reserved", ctypes.c_int32), ("max_cell_size", I64),
            ("nf_slot", P), ("refresh_nf", I64), ("gate", P), ("epoch", I64),
            ("philox_round_keys", U32 * 20), ("shuffle_only", I64),
-           ("radius", P), ("fall_velocity", P)])
+           ("radius", P), ("fall_velocity", P), ("berry_params", F64 * 13),
+           ("berry_int_mask", I64), ("berry_unit", F64)])
 
 
-KERNELS = {"Golovin": 0, "ConstantK": 1, "Linear": 2, "Geometric": 3}
+KERNELS = {"Golovin": 0, "ConstantK": 1, "Linear": 2, "Geometric": 3, "Hydrodynamic": 4}
 EW = {"add": 0, "sub": 1, "mul": 2, "div": 3, "div_if_not_zero": 4, "pow": 5, "axpy": 6,
       "floor": 7, "exp": 8, "abs": 9, "mod": 10}
 PAIR_OPS = {"distance": 0, "max": 1, "min": 2, "sum": 3, "multiply": 4}

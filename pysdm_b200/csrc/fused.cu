@@ -34,6 +34,7 @@
 // conversion/transcendental pipe (XU) long before HBM unless 64-bit int<->fp conversions,
 // fp64 divisions and ceil() are kept out of the per-SD path; see the helpers below --
 // each is exact (bit-identical to the plain expression), with a guarded slow path.
+#include "berry.cuh"
 #include "philox.cuh"
 #include "pysdm_b200.h"
 #include "sdm_device.cuh"
@@ -41,7 +42,8 @@
 // C-ABI argument block: include/pysdm_b200.h (mirrored by ctypes in pysdm_b200/_lib.py)
 typedef pysdm_b200_fused_args FusedArgs;
 
-enum { KERNEL_GOLOVIN = 0, KERNEL_CONSTANT_K = 1, KERNEL_LINEAR = 2, KERNEL_GEOMETRIC = 3 };
+enum { KERNEL_GOLOVIN = 0, KERNEL_CONSTANT_K = 1, KERNEL_LINEAR = 2, KERNEL_GEOMETRIC = 3,
+       KERNEL_HYDRODYNAMIC = 4 };
 
 #ifndef PYSDM_WARP_POS
 #define PYSDM_WARP_POS 1024
@@ -119,6 +121,29 @@ __device__ __forceinline__ double geometric_kernel_temp(double r_j, double r_k, 
     const double sgn = x > 0 ? 1.0 : (x < 0 ? -1.0 : (x == 0 ? 0.0 : x));
     double out = sgn * (fabs(x) * fabs(x));
     out = out * a;
+    return out * fabs(u_j - u_k);
+}
+
+__device__ __forceinline__ double signed_square(double x)  // Storage `**= 2`
+{
+    const double sgn = x > 0 ? 1.0 : (x < 0 ? -1.0 : (x == 0 ? 0.0 : x));
+    return sgn * (fabs(x) * fabs(x));
+}
+
+// Parameterized / Hydrodynamic (collision_kernels/impl/parameterized.py:13-30):
+// output = linear_collection_efficiency(radius pair); output **= 2; output *= PI (= a);
+// pair_tmp = max_pair(radius); pair_tmp **= 2; output *= pair_tmp;
+// pair_tmp = distance_pair(fall velocity); output *= pair_tmp
+__device__ __forceinline__ double hydrodynamic_kernel_temp(const FusedArgs &a, double r_j,
+                                                           double r_k, double u_j, double u_k)
+{
+    Berry q;
+#pragma unroll
+    for (int e = 0; e < 13; ++e) q.p[e] = a.berry_params[e];
+    q.int_mask = a.berry_int_mask;
+    double out = signed_square(berry_efficiency(q, r_j, r_k, a.berry_unit));
+    out = out * a.kernel_a;
+    out = out * signed_square(py_max(r_j, r_k));  // max(in[idx[i]], in[idx[i+1]]), pair_methods.py:57-75
     return out * fabs(u_j - u_k);
 }
 
@@ -287,8 +312,9 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     const i64 n_pairs_active = a.length / 2;
     // literal chain for a slot without a pair: max_pair -> 0; *= kernel_temp; normalize
     const double prob_nopair =
-        0.0 * (K == KERNEL_GEOMETRIC ? geometric_kernel_temp(0.0, 0.0, 0.0, 0.0, a.kernel_a)
-                                     : kernel_temp_of<K>(0.0, a.kernel_a, a.kernel_b));
+        0.0 * (K == KERNEL_GEOMETRIC || K == KERNEL_HYDRODYNAMIC
+                   ? 0.0  // zero-filled pair slots: 0 ** 2 * a * 0 ** 2 * 0
+                   : kernel_temp_of<K>(0.0, a.kernel_a, a.kernel_b));
     const bool unit_substeps = a.substeps == 1.0;
     const double rho_rcp = 1.0 / a.rho_w;
     const bool rho_ok = a.reserved != 0;  // host-checked precondition of div_by
@@ -481,7 +507,8 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
 
     // ---- phase 4: two pair slots per thread and iteration ---------------------------------
     // per-SD operand of the collision kernel: water mass, or the radius attribute (Geometric)
-    const double *mass = K == KERNEL_GEOMETRIC ? a.radius : a.attributes + a.mass_row * a.n_sd;
+    constexpr bool kGravitational = K == KERNEL_GEOMETRIC || K == KERNEL_HYDRODYNAMIC;
+    const double *mass = kGravitational ? a.radius : a.attributes + a.mass_row * a.n_sd;
     const bool flag_al = (((uintptr_t)a.is_first_in_pair) & 1) == 0;
     const bool vec_out = (((uintptr_t)a.idx_out) & 15) == 0;
     // batch-local bases (32-bit offsets in the loop); dl = local pair slot = lp0 / 2
@@ -579,7 +606,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
                     mj[h] = mass[j[h]];
                     mk[h] = mass[k[h]];
                 }
-                if (K == KERNEL_GEOMETRIC) {
+                if (kGravitational) {
                     uj[h] = a.fall_velocity[j[h]];
                     uk[h] = a.fall_velocity[k[h]];
                 }
@@ -632,6 +659,8 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
                 double kernel_temp;
                 if (K == KERNEL_GEOMETRIC) {  // |u_j - u_k| is symmetric: no need to swap uj / uk
                     kernel_temp = geometric_kernel_temp(m_j, m_k, uj[h], uk[h], a.kernel_a);
+                } else if (K == KERNEL_HYDRODYNAMIC) {
+                    kernel_temp = hydrodynamic_kernel_temp(a, m_j, m_k, uj[h], uk[h]);
                 } else {
                     double vsum = 0.0;
                     if (K != KERNEL_CONSTANT_K)
@@ -759,6 +788,9 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
     case KERNEL_GEOMETRIC:
         if (a.radius == nullptr || a.fall_velocity == nullptr) return (int)cudaErrorInvalidValue;
         return dispatch_fused<KERNEL_GEOMETRIC>(a, n_batches, philox, warp, aggregate, st);
+    case KERNEL_HYDRODYNAMIC:
+        if (a.radius == nullptr || a.fall_velocity == nullptr) return (int)cudaErrorInvalidValue;
+        return dispatch_fused<KERNEL_HYDRODYNAMIC>(a, n_batches, philox, warp, aggregate, st);
     default: return (int)cudaErrorInvalidValue;
     }
 }

@@ -19,6 +19,7 @@
 #include <math.h>
 
 #include "common.cuh"
+#include "berry.cuh"
 
 namespace {
 
@@ -28,26 +29,6 @@ constexpr double kSqrt2OverPi = 0.79788456080286535588;  // sqrt(2 / pi)
 
 __device__ __forceinline__ double sq(double x) { return x * x; }
 __device__ __forceinline__ double cube(double x) { return x * (x * x); }
-
-// Numba's `float ** int` (numba/cpython/numbers.py:214-245): square and multiply
-__device__ __forceinline__ double int_power(double a, i64 b)
-{
-    double r = 1.0;
-    bool invert = b < 0;
-    i64 e = invert ? -b : b;
-    if (e > 0x10000) return pow(a, (double)b);
-    while (e != 0) {
-        if (e & 1) r *= a;
-        e >>= 1;
-        a *= a;
-    }
-    return invert ? 1.0 / r : r;
-}
-
-__device__ __forceinline__ double pw(double x, double e, bool is_int)
-{
-    return is_int ? int_power(x, (i64)e) : pow(x, e);
-}
 
 // physics/trivia.py:95-108 (Vedder 1987), constants_defaults.py:364-366
 __device__ __forceinline__ double erfinv_approx(double c)
@@ -137,10 +118,6 @@ __global__ void k_power_series(double *__restrict__ values, const double *__rest
 }
 
 // ---- linear_collection_efficiency ----------------------------------------------------
-struct Berry {
-    double p[13];
-    i64 int_mask;
-};
 __global__ void k_linear_collection_efficiency(Berry q, double *__restrict__ output, i64 out_len,
                                                const double *__restrict__ radii,
                                                const u8 *__restrict__ flag,
@@ -153,26 +130,7 @@ __global__ void k_linear_collection_efficiency(Berry q, double *__restrict__ out
     for (int s = 0; s < 2; ++s) {
         i64 pos = 2 * i + s;
         if (pos >= length - 1 || !flag[pos]) continue;
-        double ra = radii[idx[pos]], rb = radii[idx[pos + 1]];
-        double r, r_s;
-        if (ra > rb) {
-            r = ra / unit;
-            r_s = rb / unit;
-        } else {
-            r = rb / unit;
-            r_s = ra / unit;
-        }
-        double p = r_s / r;
-        if (p != 0 && p != 1) {
-            double G = pw(q.p[8] / r, q.p[12], (q.int_mask >> 12) & 1) + q.p[9] + q.p[10] * r;
-            double Gp = pow(1 - p, G);
-            if (Gp != 0) {
-                double D = q.p[2] / pw(r, q.p[3], (q.int_mask >> 3) & 1);
-                double E = q.p[4] / pw(r, q.p[5], (q.int_mask >> 5) & 1);
-                double F = pw(q.p[6] / r, q.p[11], (q.int_mask >> 11) & 1) + q.p[7];
-                o = py_max(0.0, q.p[0] + q.p[1] * p + D / pow(p, F) + E / Gp);
-            }
-        }
+        o = berry_efficiency(q, radii[idx[pos]], radii[idx[pos + 1]], unit);
     }
     output[i] = o;
 }

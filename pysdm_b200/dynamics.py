@@ -11,7 +11,7 @@ It derives from the reference's own class (PySDM/dynamics/collisions/collision.p
 `Coalescence` :293-330), registers under the same name ("Collision"), allocates the same
 storages, and overrides `step()` only: when the configuration is one the fused kernel
 covers -- B200 backend, non-adaptive, "local" croupier, Golovin / ConstantK / Linear /
-Geometric kernel,
+Geometric / Hydrodynamic kernel,
 no breakup, every cell within the fused kernel's size limit, `optimized_random` off -- one
 launch replaces the sequence `Collision.step` issues (:196-234) and writes every storage
 that sequence writes (idx, pair flags, gamma, multiplicities, attributes, norm factors, rate
@@ -31,8 +31,15 @@ def _geometric(k):
     return (const.PI * k.collection_efficiency, 0.0)
 
 
+def _parameterized(k):  # collision_kernels/impl/parameterized.py:23: `output *= const.PI`
+    from PySDM.physics import constants as const  # pylint: disable=import-outside-toplevel
+
+    return (const.PI, 0.0)
+
+
 _KERNELS = {"Golovin": lambda k: (0.0, k.b), "ConstantK": lambda k: (k.a, 0.0),
-            "Linear": lambda k: (k.a, k.b), "Geometric": _geometric}
+            "Linear": lambda k: (k.a, k.b), "Geometric": _geometric,
+            "Hydrodynamic": _parameterized}
 
 
 def make_fused_coalescence():
@@ -95,7 +102,12 @@ def make_fused_coalescence():
             else:  # injected uniforms (parity runs with the Numba backend's stream)
                 pairs_rand, rand = self.rnd_opt_coll.get_random_arrays()
                 kw = {"u01": pairs_rand.data, "rand": rand.data}
-            if name == "Geometric":
+            if name == "Hydrodynamic":  # Berry's parameterization, parameterized.py:14-20
+                from PySDM.physics import constants as const  # pylint: disable=import-outside-toplevel
+
+                kw["berry_params"] = self.collision_kernel.params
+                kw["berry_unit"] = const.si.um
+            if name in ("Geometric", "Hydrodynamic"):
                 # dependent attributes, recomputed by the orchestration when the water mass was
                 # marked updated (attributes/physics/radius.py:15-17, relative_fall_velocity.py,
                 # terminal_velocity.py) -- the operands geometric.py:15-22 gathers

@@ -259,11 +259,13 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
                          max_cell, kernel, kernel_a=0.0, kernel_b=0.0, timestep, dv, rho_w,
                          substeps=1, mass_row=0, u01=None, rand=None, seed=0, call_u01=0,
                          call_rand=0, nf_slot, refresh_nf=True, gate=None, epoch=1, radius=None,
-                         fall_velocity=None):
+                         fall_velocity=None, berry_params=None, berry_unit=1.0):
     """one Collision.step() in one launch; returns the CUDA error code (9 = a cell is
     larger than the fused path supports -> use the method-level functions).  kernel
     "Geometric": kernel_a = PI * collection_efficiency, `radius` and `fall_velocity` = the
-    per-SD attributes of that name (f64[n_sd])"""
+    per-SD attributes of that name (f64[n_sd]); kernel "Hydrodynamic" (any `Parameterized`
+    kernel): kernel_a = PI, the same two arrays, `berry_params` = the 13 parameters as passed to
+    linear_collection_efficiency (ints kept as ints), `berry_unit` = its `unit`"""
     n_attr, n_sd = attributes.shape
     args = _lib.FusedArgs(
         idx_in=_pi(idx_in), idx_out=_pi(idx_out), cell_start=_pi(cell_start),
@@ -279,6 +281,11 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         kernel_b=float(kernel_b), kernel=_lib.KERNELS[kernel], reserved=0,
         max_cell_size=int(max_cell), nf_slot=_pf(nf_slot), refresh_nf=int(bool(refresh_nf)),
         gate=_pi(gate), epoch=int(epoch), radius=_pf(radius), fall_velocity=_pf(fall_velocity))
+    if berry_params is not None:
+        assert len(berry_params) == 13
+        args.berry_params = (ctypes.c_double * 13)(*[float(v) for v in berry_params])
+        args.berry_int_mask = int_mask_of(berry_params)
+        args.berry_unit = float(berry_unit)
     return _lib.load().pysdm_b200_fused_collision_step(ctypes.byref(args), _stream())
 
 

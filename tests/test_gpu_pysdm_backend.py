@@ -417,9 +417,11 @@ def test_relaxed_velocity_dynamic(pysdm, constant):
 
 @pytest.mark.parametrize("host_rng", (True, False))
 @pytest.mark.parametrize("grid", ((1,), (4, 5)))
-def test_fused_coalescence_geometric(pysdm, grid, host_rng):
-    """`FusedCoalescence` with the Geometric (gravitational) kernel, collision_kernels/
-    geometric.py:15-22: the fused kernel gathers the orchestration's own "radius" and "relative
+@pytest.mark.parametrize("kernel", ("Geometric", "Hydrodynamic"))
+def test_fused_coalescence_geometric(pysdm, kernel, grid, host_rng):
+    """`FusedCoalescence` with the gravitational kernels -- Geometric, collision_kernels/
+    geometric.py:15-22, and Hydrodynamic (Berry's collection efficiency, impl/parameterized.py:
+    13-30): the fused kernel gathers the orchestration's own "radius" and "relative
     fall velocity" attributes.  host_rng=False: against the stock dynamic on the B200 backend,
     same device Philox stream -- everything bit-identical.  host_rng=True: against the Numba
     backend with the same uniforms -- integers / permutation / gamma identical, attributes to
@@ -427,7 +429,7 @@ def test_fused_coalescence_geometric(pysdm, grid, host_rng):
     from PySDM import Builder, Formulae  # pylint: disable=import-outside-toplevel
     from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
     from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
-    from PySDM.dynamics.collisions.collision_kernels import Geometric  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics.collisions.collision_kernels import Geometric, Hydrodynamic  # pylint: disable=import-outside-toplevel
     from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
     from PySDM.impl.mesh import Mesh  # pylint: disable=import-outside-toplevel
 
@@ -447,8 +449,10 @@ def test_fused_coalescence_geometric(pysdm, grid, host_rng):
         if n_cell > 1:
             env.mesh = Mesh(grid, size=grid, dv=0.05 / n_cell)
         builder = Builder(n_sd=n_sd, backend=backend, environment=env)
-        builder.add_dynamic(dynamic(collision_kernel=Geometric(collection_efficiency=0.9),
-                                    adaptive=False, croupier="local"))
+        collision_kernel = Geometric(collection_efficiency=0.9) if kernel == "Geometric" \
+            else Hydrodynamic()
+        builder.add_dynamic(dynamic(collision_kernel=collision_kernel, adaptive=False,
+                                    croupier="local"))
         return builder.build(attributes={k: v.copy() for k, v in attributes.items()}, products=())
 
     fkw = dict(fastmath=False, seed=31)

@@ -217,6 +217,24 @@ typedef struct pysdm_b200_fused_args {
     double berry_params[13];     /* kernel 4: (A, B, D1, D2, E1, E2, F1, F2, G1, G2, G3, Mf, Mg) as */
     int64_t berry_int_mask;      /* in pysdm_b200_linear_collection_efficiency */
     double berry_unit;
+    /* ---- adaptive time step (Collision.__call__ sub-step loop, collision.py:174-194; one launch =
+     * one sub-step incl. scale_prob_for_adaptive_sdm_gamma, collisions_methods.py:330-405) ---- */
+    int64_t adaptive;            /* != 0: the fields below are used, `substeps` is ignored */
+    double *dt_left;             /* [n_cell] by cell id: -= dt_todo */
+    int64_t *stats_n_substep;    /* [n_cell] by cell id: += (dt_todo > 0) */
+    double *stats_dt_min;        /* [n_cell] by cell id: min with the pairs' dt_optimal (NaN sticks) */
+    double dt_min, dt_max;       /* dt_coal_range */
+    const int64_t *rank_to_cell; /* [n_cell] cell id held by rank r of cell_start, i.e. the inverse of
+                                    the cell_idx the LAST sort by cell used (cell_idx itself is
+                                    re-sorted every sub-step without a re-sort of idx, quirk A2) */
+    int64_t *rank_info;          /* [n_cell] scratch: cell id | parity of cell_start[cell_idx[cell id]]
+                                    << 62, rebuilt by every adaptive launch */
+    int64_t *adaptive_end;       /* [2] or NULL: [0] = max over cells i with dt_left[i] != 0 after
+                                    this sub-step of cell_start[i + 1] (adaptive_sdm_end, :313-328;
+                                    zeroed by the launch), [1] = 1 if some stats_dt_min == dt_min */
+    const int64_t *length_dev;   /* [1] or NULL: working length read on the device instead of
+                                    `length` (the adaptive_end[0] of the previous sub-step); a
+                                    launch that finds 0 there does nothing */
 } pysdm_b200_fused_args;
 
 int64_t pysdm_b200_fused_max_cell_size(void);
@@ -228,6 +246,9 @@ int pysdm_b200_shuffle_local_batched(int64_t *idx, const double *u01, const int6
                                      int64_t n_cell, int64_t n_sd, int64_t max_cell_size,
                                      int64_t *status, void *stream);
 int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *host_args, void *stream);
+/* out[in[c]] = c for c < n: the rank -> cell map (`rank_to_cell` above) of the cell -> rank map
+ * `cell_idx` a sort by cell has just used (collisions_methods.py:692-697 consume it that way) */
+int pysdm_b200_invert_index(int64_t *out, const int64_t *in, int64_t n, void *stream);
 
 /* ---- terminal velocities: methods/terminal_velocity_methods.py ----------------------- */
 

@@ -55,6 +55,7 @@ SIGNATURES = {
     "pysdm_b200_fused_max_cell_size": (I64, ()),
     "pysdm_b200_fused_collision_step": (INT, (P, P)),
     "pysdm_b200_shuffle_local_batched": (INT, (P, P, P, I64, I64, I64, P, P)),
+    "pysdm_b200_invert_index": (INT, (P, P, I64, P)),
     "pysdm_b200_interpolation": (INT, (P, P, I64, F64, P, P, P)),
     "pysdm_b200_terminal_velocity_rogers_yau": (INT, (P, P, I64, F64, F64, F64, F64, F64, P)),
     "pysdm_b200_power_series": (INT, (P, P, I64, I64, P, P, P)),
@@ -103,7 +104,10 @@ class FusedArgs(ctypes.Structure):
            ("nf_slot", P), ("refresh_nf", I64), ("gate", P), ("epoch", I64),
            ("philox_round_keys", U32 * 20), ("shuffle_only", I64),
            ("radius", P), ("fall_velocity", P), ("berry_params", F64 * 13),
-           ("berry_int_mask", I64), ("berry_unit", F64)])
+           ("berry_int_mask", I64), ("berry_unit", F64),
+           ("adaptive", I64), ("dt_left", P), ("stats_n_substep", P), ("stats_dt_min", P),
+           ("dt_min", F64), ("dt_max", F64), ("rank_to_cell", P), ("rank_info", P),
+           ("adaptive_end", P), ("length_dev", P)])
 
 
 KERNELS = {"Golovin": 0, "ConstantK": 1, "Linear": 2, "Geometric": 3, "Hydrodynamic": 4}

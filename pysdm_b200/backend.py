@@ -61,6 +61,9 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
         self.device = torch.device(device)
         if host_rng:  # parity runs: the Numba backend's PCG64 stream, uploaded
             self.Random = HostReplayRandom
+        # cell caretakers made by this backend, by the device pointer of the cell_start they
+        # last sorted into (weak references: a caretaker lives as long as its ParticleAttributes)
+        self._caretakers = {}
         BackendMethods.__init__(self)
 
     @property
@@ -76,17 +79,24 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
     def shuffle_global(idx, length, u01):  # :22-30
         m.shuffle_global(idx, int(length), u01)
 
-    # what the last sort by cell learnt about `cell_start` (keyed by its device pointer): the
-    # working length and the largest cell, so that shuffle_local needs no device sync and
-    # can pick the one-launch shuffle for populations of small cells
-    _cell_start_facts = {}  # id(tensor) -> (weakref to the tensor, length, largest cell)
+    def sort_facts(self, cell_start):
+        """the caretaker whose last sort by cell wrote the device tensor `cell_start` (it knows
+        the sorted length, the largest cell and the rank -> cell map), or None"""
+        ref = self._caretakers.get(cell_start.data_ptr())
+        caretaker = ref() if ref is not None else None
+        if caretaker is None or caretaker.cell_start_ref() is not cell_start:
+            return None
+        return caretaker
 
-    @staticmethod
-    def shuffle_local(idx, u01, cell_start):  # :32-44
-        ref, length, max_cell = B200._cell_start_facts.get(id(cell_start), (None, None, None))
-        if ref is None or ref() is not cell_start:  # not (or no longer) the tensor that was sorted
-            length = max_cell = None
-        m.shuffle_local(idx, u01, cell_start, length, max_cell)
+    def shuffle_local(self, idx, u01, cell_start):  # :32-44
+        # what the last sort by cell learnt about `cell_start`: the working length and the largest
+        # cell, so that no device sync is needed and populations of small cells take the
+        # one-launch shuffle
+        facts = self.sort_facts(cell_start)
+        if facts is None:
+            m.shuffle_local(idx, u01, cell_start, None, None)
+        else:
+            m.shuffle_local(idx, u01, cell_start, facts.length, facts.max_cell)
 
     @staticmethod
     def sort_by_key(idx, attr):  # :46-48
@@ -100,23 +110,33 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
     def cell_id(cell_id, cell_origin, strides):  # collisions_methods.py:407-416
         m.cell_id(cell_id.data, cell_origin.data, strides.data)
 
-    @staticmethod
-    def make_cell_caretaker(idx_shape, idx_dtype, cell_start_len, scheme="default"):
+    def make_cell_caretaker(self, idx_shape, idx_dtype, cell_start_len, scheme="default"):
         """collisions_methods.py:587-631: owns tmp_idx, swaps the .data of idx and tmp_idx"""
-        class CellCaretaker:  # pylint: disable=too-few-public-methods
+        registry = self._caretakers
+
+        class CellCaretaker:  # pylint: disable=too-few-public-methods,too-many-instance-attributes
             def __init__(self):
                 self.scheme = scheme
                 self.tmp_idx = Storage.empty(idx_shape, idx_dtype)
+                # facts of the last sort (for shuffle_local and the fused step)
+                self.length = self.max_cell = None
+                self.cell_start_ref = lambda: None
+                self.n_sorts = 0
+                self.rank_to_cell = torch.arange(cell_start_len - 1, dtype=torch.int64,
+                                                 device=self.tmp_idx.data.device)
 
             def __call__(self, cell_id, cell_idx, cell_start, idx):
                 m.counting_sort_by_cell_id(self.tmp_idx.data, idx.data, cell_id.data,
                                            cell_idx.data, len(idx), cell_start.data)
                 idx.data, self.tmp_idx.data = self.tmp_idx.data, idx.data
-                facts = B200._cell_start_facts
-                for key in [k for k, v in facts.items() if v[0]() is None]:
-                    del facts[key]  # tensors that are gone
-                facts[id(cell_start.data)] = (weakref.ref(cell_start.data), len(idx),
-                                              m.max_cell_size(cell_start.data))
+                m.invert_index(self.rank_to_cell, cell_idx.data)
+                self.length = int(len(idx))
+                self.max_cell = m.max_cell_size(cell_start.data)
+                self.cell_start_ref = weakref.ref(cell_start.data)
+                self.n_sorts += 1
+                for key in [k for k, v in registry.items() if v() is None]:
+                    del registry[key]  # caretakers that are gone
+                registry[cell_start.data.data_ptr()] = weakref.ref(self)
 
         assert cell_start_len >= 1
         return CellCaretaker()

@@ -11,9 +11,10 @@ identical to `Builder(...).build(...)` + `particulator.run()` under the referenc
 
 Two execution modes over the same state:
   * method level -- one CUDA kernel (group) per reference backend method (pysdm_b200.methods);
-  * fused        -- one launch per step (csrc/fused.cu) for non-adaptive Coalescence with the
-                    "local" croupier and a Golovin / ConstantK / Linear kernel, when every cell
-                    fits a CTA batch.  Selected automatically; bit-identical to the first mode.
+  * fused        -- one launch per (sub-)step (csrc/fused*.cu) for Coalescence with the "local"
+                    croupier and a Golovin / ConstantK / Linear kernel, adaptive time step
+                    included, when every cell fits a CTA batch.  Selected automatically;
+                    bit-identical to the first mode.
 There is no CPU path.
 """
 
@@ -103,7 +104,14 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.sorted = False
         self.sorted_length = 0
         self.max_cell = None
-        self.healthy = full(1, 1, i64)
+        # words the host reads back after a step: [0] healthy, [1:3] the fused adaptive
+        # sub-step's adaptive_sdm_end result (pysdm_b200.h `adaptive_end`)
+        self._words = full(4, 0, i64)
+        self.healthy = self._words[0:1]
+        self.healthy.fill_(1)
+        self.adaptive_end = self._words[1:3]
+        self.rank_to_cell = torch.arange(self.n_cell, dtype=i64, device=dev)
+        self.rank_info = full(self.n_cell, 0, i64)
         # Collision.register (collision.py:101-172)
         n_pairs = self.n_sd // 2
         nan = float("nan")
@@ -135,6 +143,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.n_fused_steps = 0
         self.n_launches = 0  # CUDA launches issued through the C-ABI (entry-point calls)
         self._healthy_host = torch.ones(1, dtype=i64).pin_memory()
+        self._words_host = torch.zeros(4, dtype=i64).pin_memory()
         # speculative stepping (step_async): gate word of the fused kernel, two pinned slots
         # for the `healthy` flags in flight, the step whose flag has not been read yet
         self.gate = full(1, 0, i64)
@@ -154,6 +163,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         m.counting_sort_by_cell_id(self.tmp_idx, self.idx, self.cell_id, self.cell_idx,
                                    self.length, self.cell_start)
         self.idx, self.tmp_idx = self.tmp_idx, self.idx
+        m.invert_index(self.rank_to_cell, self.cell_idx)  # the cell each rank of cell_start holds
         self.sorted = True
         self.sorted_length = self.length  # = cell_start[-1], kept on the host
         self.max_cell = None
@@ -228,8 +238,21 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             self.dt_left.fill_(self.dt)
             while self.length != 0:
                 m.sort_by_key(self.cell_idx, self.dt_left)
-                self.step()
-                end = m.adaptive_sdm_end(self.dt_left, self.get_cell_start())
+                if self._fused_ok():
+                    # the launch also leaves adaptive_sdm_end's result next to `healthy`: one
+                    # read-back per sub-step (valid unless SDs were removed: the reference then
+                    # re-sorts by cell before adaptive_sdm_end looks at cell_start)
+                    self.step_fused()
+                    self._words_host.copy_(self._words, non_blocking=True)
+                    torch.cuda.current_stream().synchronize()
+                    if self._words_host[0]:
+                        end = int(self._words_host[1])
+                    else:
+                        self._remove_zero_multiplicities()
+                        end = m.adaptive_sdm_end(self.dt_left, self.get_cell_start())
+                else:
+                    self.step()
+                    end = m.adaptive_sdm_end(self.dt_left, self.get_cell_start())
                 assert end <= self.length
                 self.length = end
             self.length = self.valid_n_sd
@@ -248,9 +271,9 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.drain()
 
     def _fused_ok(self):
-        if self.fused is False or self.adaptive or self.croupier != "local":
+        if self.fused is False or self.croupier != "local":
             return False
-        if getattr(self.kernel, "fused", None) is None or self.optimized_random:
+        if getattr(self.kernel, "fused", None) is None:
             return False
         self.get_cell_start()
         if self.max_cell is None:
@@ -315,12 +338,19 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
     def step_fused(self, gated=False):
         """one launch: csrc/fused.cu"""
         kw = {}
-        if isinstance(self.rnd, Random):  # uniforms generated in-kernel from the same stream
-            kw = {"seed": self.rnd.seed, "call_u01": self.rnd.call, "call_rand": self.rnd.call + 1}
+        if self.adaptive:
+            kw["adaptive"] = {
+                "dt_left": self.dt_left, "stats_n_substep": self.stats_n_substep,
+                "stats_dt_min": self.stats_dt_min, "dt_min": self.dt_coal_range[0],
+                "dt_max": self.dt_coal_range[1], "rank_to_cell": self.rank_to_cell,
+                "rank_info": self.rank_info, "adaptive_end": self.adaptive_end}
+        if isinstance(self.rnd, Random) and not self.optimized_random:
+            # uniforms generated in-kernel from the same stream
+            kw.update(seed=self.rnd.seed, call_u01=self.rnd.call, call_rand=self.rnd.call + 1)
             self.rnd.call += 2
         else:
             pairs_rand, rand = self.get_random_arrays()
-            kw = {"u01": pairs_rand, "rand": rand}
+            kw.update(u01=pairs_rand, rand=rand)
         err = m.fused_collision_step(
             idx_in=self.idx, idx_out=self.tmp_idx, cell_start=self.cell_start,
             cell_idx=self.cell_idx, cell_id_=self.cell_id, multiplicity=self.multiplicity,
@@ -330,15 +360,15 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             coalescence_rate=self.coalescence_rate, healthy=self.healthy, status=self.status,
             length=self.length, max_cell=self.max_cell, kernel=self.kernel.fused,
             kernel_a=self.kernel.a, kernel_b=self.kernel.b, timestep=self.dt, dv=self.dv,
-            rho_w=self.rho_w, substeps=self.substeps, nf_slot=self.nf_slot,
-            refresh_nf=not self.nf_valid, gate=self.gate if gated else None,
+            rho_w=self.rho_w, substeps=1 if self.adaptive else self.substeps,
+            nf_slot=self.nf_slot, refresh_nf=not self.nf_valid, gate=self.gate if gated else None,
             epoch=self.n_fused_steps + 1, **kw)
         m.check(err, "fused_collision_step")
-        self.n_launches += 1 if self.nf_valid else 3
-        self.nf_valid = True
-        # positions beyond the working length keep their content (flagged SDs)
-        if self.length < self.n_sd:
-            self.tmp_idx[self.length:] = self.idx[self.length:]
+        self.n_launches += 1 if self.nf_valid and not self.adaptive else 3
+        self.nf_valid = not self.adaptive  # (cell_idx is re-sorted before every adaptive sub-step)
+        # positions beyond the sorted range keep their content (flagged SDs)
+        if self.sorted_length < self.n_sd:
+            self.tmp_idx[self.sorted_length:] = self.idx[self.sorted_length:]
         self.idx, self.tmp_idx = self.tmp_idx, self.idx
         self.n_fused_steps += 1
 

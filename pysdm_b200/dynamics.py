@@ -1,5 +1,5 @@
 """`FusedCoalescence`: PySDM's `Coalescence` dynamic with `step()` mapped onto the one-launch
-fused kernel (csrc/fused.cu) -- for users of the unchanged PySDM orchestration
+fused kernel (csrc/fused*.cu) -- for users of the unchanged PySDM orchestration
 (`Builder`, `Particulator`, attributes, products) who want the collision step at the speed
 `bench.py` measures instead of ~15 backend calls per step:
 
@@ -10,19 +10,25 @@ fused kernel (csrc/fused.cu) -- for users of the unchanged PySDM orchestration
 It derives from the reference's own class (PySDM/dynamics/collisions/collision.py:46-290,
 `Coalescence` :293-330), registers under the same name ("Collision"), allocates the same
 storages, and overrides `step()` only: when the configuration is one the fused kernel
-covers -- B200 backend, non-adaptive, "local" croupier, Golovin / ConstantK / Linear /
-Geometric / Hydrodynamic kernel,
-no breakup, every cell within the fused kernel's size limit, `optimized_random` off -- one
-launch replaces the sequence `Collision.step` issues (:196-234) and writes every storage
-that sequence writes (idx, pair flags, gamma, multiplicities, attributes, norm factors, rate
-counters, `healthy`), bit for bit (tests/test_gpu_pysdm_backend.py).  Anything else falls
-through to the reference's `step()` and the method-level kernels.
+covers -- B200 backend, "local" croupier, Golovin / ConstantK / Linear / Geometric /
+Hydrodynamic kernel, no breakup, every cell within the fused kernel's size limit; fixed
+sub-steps or the adaptive time step, with or without `optimized_random` -- one launch replaces
+the sequence `Collision.step` issues (:196-234) and writes every storage that sequence writes
+(idx, pair flags, gamma, multiplicities, attributes, norm factors, rate counters, `healthy`,
+and for the adaptive time step `dt_left`, `stats_n_substep`, `stats_dt_min`), bit for bit
+(tests/test_gpu_pysdm_backend.py).  The adaptive loop itself (`Collision.__call__`, :174-194:
+sort of `cell_idx` by `dt_left`, `adaptive_sdm_end`, the working-length cut) stays the
+reference's.  Anything else falls through to the reference's `step()` and the method-level
+kernels.
 """
+
+import warnings
 
 import torch
 
 from . import methods as m
 from .random import Random
+
 
 def _geometric(k):
     """collision_kernels/geometric.py:18: the factor `output *= const.PI * collection_efficiency`"""
@@ -52,7 +58,7 @@ def make_fused_coalescence():
         def __init__(self, *args, **kwargs):
             super().__init__(*args, **kwargs)
             self.n_fused_steps = 0
-            self._nf_slot = self._status = self._nf_facts = None
+            self._nf_slot = self._status = self._nf_facts = self._rank_info = None
 
         def register(self, builder):
             super().register(builder)
@@ -60,20 +66,31 @@ def make_fused_coalescence():
             self._nf_slot = torch.full((self.particulator.n_sd // 2,), float("nan"),
                                        dtype=torch.float64, device=dev)
             self._status = torch.zeros(1, dtype=torch.int64, device=dev)
+            self._rank_info = torch.zeros(self.particulator.mesh.n_cell, dtype=torch.int64,
+                                          device=dev)
+
+        def __call__(self):
+            fused_before = self.n_fused_steps
+            super().__call__()
+            if self.adaptive and self.n_fused_steps > fused_before:
+                # the reference looks at this after every sub-step (collision.py:276-277); the
+                # fused sub-steps leave it to one look per time step (stats_dt_min only falls)
+                if self.stats_dt_min.amin() == self.dt_coal_range[0]:
+                    warnings.warn("adaptive time-step reached dt_min")
 
         def _fused_plan(self):
-            """(kernel name, a, b, facts of the current sort) or None"""
+            """(kernel name, a, b, caretaker of the current sort) or None"""
             part = self.particulator
             name = type(self.collision_kernel).__name__
-            if (not isinstance(part.backend, B200) or self.adaptive or self.enable_breakup
+            if (not isinstance(part.backend, B200) or self.enable_breakup
                     or self.croupier != "local" or name not in _KERNELS
-                    or self.rnd_opt_coll.optimized_random or part.n_sd >= 2 ** 32):
+                    or part.n_sd >= 2 ** 32
+                    or getattr(part.backend.formulae.particle_shape_and_density, "__name__",
+                               "LiquidSpheres") != "LiquidSpheres"):
                 return None
             cell_start = part.attributes.cell_start  # sorts by cell when needed
-            facts = B200._cell_start_facts.get(id(cell_start.data))  # pylint: disable=protected-access
-            if facts is None or facts[0]() is not cell_start.data:
-                return None
-            if facts[2] > m.fused_max_cell_size():
+            facts = part.backend.sort_facts(cell_start.data)
+            if facts is None or facts.max_cell > m.fused_max_cell_size():
                 return None
             return (name, *_KERNELS[name](self.collision_kernel), facts)
 
@@ -88,18 +105,19 @@ def make_fused_coalescence():
             # (PySDM/particulator.py:174-176)
             idx = attrs._ParticleAttributes__idx  # pylint: disable=protected-access
             healthy = attrs._ParticleAttributes__healthy_memory  # pylint: disable=protected-access
-            caretaker = attrs._ParticleAttributes__cell_caretaker  # pylint: disable=protected-access
             keys = attrs._ParticleAttributes__extensive_keys  # pylint: disable=protected-access
             mass_row = keys.get("signed water mass", keys.get("water mass"))
             if mass_row is None:
                 super().step()
                 return
             rnd = self.rnd_opt_coll.rnd
-            if isinstance(rnd, Random):  # device Philox: generated inside the kernel
+            if isinstance(rnd, Random) and not self.rnd_opt_coll.optimized_random:
+                # device Philox: generated inside the kernel
                 kw = {"seed": rnd.seed, "call_u01": rnd.call, "call_rand": rnd.call + 1}
                 rnd.call += 2
                 self.rnd_opt_coll.substep += 1
-            else:  # injected uniforms (parity runs with the Numba backend's stream)
+            else:  # injected uniforms (parity runs with the Numba backend's stream), or the
+                # arrays `optimized_random` fills once per time step and reads through shifted views
                 pairs_rand, rand = self.rnd_opt_coll.get_random_arrays()
                 kw = {"u01": pairs_rand.data, "rand": rand.data}
             if name == "Hydrodynamic":  # Berry's parameterization, parameterized.py:14-20
@@ -113,26 +131,35 @@ def make_fused_coalescence():
                 # terminal_velocity.py) -- the operands geometric.py:15-22 gathers
                 kw["radius"] = attrs["radius"].data
                 kw["fall_velocity"] = attrs["relative fall velocity"].data
+            substeps = 1
+            if self.adaptive:
+                kw["adaptive"] = {
+                    "dt_left": self.dt_left.data, "stats_n_substep": self.stats_n_substep.data,
+                    "stats_dt_min": self.stats_dt_min.data, "dt_min": self.dt_coal_range[0],
+                    "dt_max": self.dt_coal_range[1], "rank_to_cell": facts.rank_to_cell,
+                    "rank_info": self._rank_info}
+            else:
+                substeps = self._Collision__substeps  # pylint: disable=no-member
             length = len(idx)
             ext = attrs.get_extensive_attribute_storage()
-            substeps = self._Collision__substeps  # pylint: disable=no-member
+            sort_id = (facts, facts.n_sorts)
             err = m.fused_collision_step(
-                idx_in=idx.data, idx_out=caretaker.tmp_idx.data, cell_start=attrs.cell_start.data,
+                idx_in=idx.data, idx_out=facts.tmp_idx.data, cell_start=attrs.cell_start.data,
                 cell_idx=attrs.cell_idx.data, cell_id_=attrs["cell id"].data,
                 multiplicity=attrs["multiplicity"].data, attributes=ext.data,
                 is_first_in_pair=self.is_first_in_pair.indicator.data, gamma=self.gamma.data,
                 norm_factor=self.norm_factor_temp.data, collision_rate=self.collision_rate.data,
                 collision_rate_deficit=self.collision_rate_deficit.data,
                 coalescence_rate=self.coalescence_rate.data, healthy=healthy.data,
-                status=self._status, length=length, max_cell=facts[2], kernel=name,
+                status=self._status, length=length, max_cell=facts.max_cell, kernel=name,
                 kernel_a=kernel_a, kernel_b=kernel_b, timestep=part.dt, dv=part.mesh.dv,
                 rho_w=part.backend.rho_w, substeps=substeps, mass_row=mass_row,
-                nf_slot=self._nf_slot, refresh_nf=self._nf_facts is not facts, **kw)
+                nf_slot=self._nf_slot, refresh_nf=self._nf_facts != sort_id, **kw)
             m.check(err, "fused_collision_step")
-            self._nf_facts = facts
-            if length < idx.data.numel():  # flagged positions beyond the working length stay
-                caretaker.tmp_idx.data[length:] = idx.data[length:]
-            idx.data, caretaker.tmp_idx.data = caretaker.tmp_idx.data, idx.data
+            self._nf_facts = sort_id
+            if facts.length < idx.data.numel():  # flagged positions beyond the sorted range stay
+                facts.tmp_idx.data[facts.length:] = idx.data[facts.length:]
+            idx.data, facts.tmp_idx.data = facts.tmp_idx.data, idx.data
             self.is_first_in_pair.length = length
             self.n_fused_steps += 1
             # Particulator.collision_coalescence_breakup, PySDM/particulator.py:210-213

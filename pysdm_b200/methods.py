@@ -139,6 +139,12 @@ def cell_id(cell_id_out, cell_origin, strides):
                                          n_sd, _stream()), "cell_id")
 
 
+def invert_index(out, index):
+    """out[index[c]] = c: rank -> cell map of the cell -> rank map a sort by cell used"""
+    check(_lib.load().pysdm_b200_invert_index(_pi(out), _pi(index), index.numel(), _stream()),
+          "invert_index")
+
+
 # ---- pair methods ---------------------------------------------------------------------
 def find_pairs(cell_start, is_first_in_pair, cell_id_, cell_idx, idx, length):
     check(_lib.load().pysdm_b200_find_pairs(_pi(cell_start), _pb(is_first_in_pair), _pi(cell_id_),
@@ -259,13 +265,16 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
                          max_cell, kernel, kernel_a=0.0, kernel_b=0.0, timestep, dv, rho_w,
                          substeps=1, mass_row=0, u01=None, rand=None, seed=0, call_u01=0,
                          call_rand=0, nf_slot, refresh_nf=True, gate=None, epoch=1, radius=None,
-                         fall_velocity=None, berry_params=None, berry_unit=1.0):
+                         fall_velocity=None, berry_params=None, berry_unit=1.0, adaptive=None):
     """one Collision.step() in one launch; returns the CUDA error code (9 = a cell is
     larger than the fused path supports -> use the method-level functions).  kernel
     "Geometric": kernel_a = PI * collection_efficiency, `radius` and `fall_velocity` = the
     per-SD attributes of that name (f64[n_sd]); kernel "Hydrodynamic" (any `Parameterized`
     kernel): kernel_a = PI, the same two arrays, `berry_params` = the 13 parameters as passed to
-    linear_collection_efficiency (ints kept as ints), `berry_unit` = its `unit`"""
+    linear_collection_efficiency (ints kept as ints), `berry_unit` = its `unit`.
+    `adaptive`: None, or a dict with the fields of the adaptive block of pysdm_b200_fused_args
+    (dt_left, stats_n_substep, stats_dt_min, dt_min, dt_max, rank_to_cell, rank_info and
+    optionally adaptive_end, length_dev): the launch is then one sub-step of the adaptive loop"""
     n_attr, n_sd = attributes.shape
     args = _lib.FusedArgs(
         idx_in=_pi(idx_in), idx_out=_pi(idx_out), cell_start=_pi(cell_start),
@@ -281,6 +290,16 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         kernel_b=float(kernel_b), kernel=_lib.KERNELS[kernel], reserved=0,
         max_cell_size=int(max_cell), nf_slot=_pf(nf_slot), refresh_nf=int(bool(refresh_nf)),
         gate=_pi(gate), epoch=int(epoch), radius=_pf(radius), fall_velocity=_pf(fall_velocity))
+    if adaptive is not None:
+        args.adaptive = 1
+        args.dt_left = _pf(adaptive["dt_left"])
+        args.stats_n_substep = _pi(adaptive["stats_n_substep"])
+        args.stats_dt_min = _pf(adaptive["stats_dt_min"])
+        args.dt_min, args.dt_max = float(adaptive["dt_min"]), float(adaptive["dt_max"])
+        args.rank_to_cell = _pi(adaptive["rank_to_cell"])
+        args.rank_info = _pi(adaptive["rank_info"])
+        args.adaptive_end = _pi(adaptive.get("adaptive_end"))
+        args.length_dev = _pi(adaptive.get("length_dev"))
     if berry_params is not None:
         assert len(berry_params) == 13
         args.berry_params = (ctypes.c_double * 13)(*[float(v) for v in berry_params])

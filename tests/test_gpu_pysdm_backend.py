@@ -137,7 +137,8 @@ def test_b200_backend_equals_numba_backend(pysdm, case):
 
 
 @pytest.mark.parametrize("host_rng", (True, False))
-@pytest.mark.parametrize("case", ("local", "substeps", "box", "global"))
+@pytest.mark.parametrize("case", ("local", "substeps", "box", "global", "adaptive",
+                                  "adaptive_optrand"))
 def test_fused_coalescence_dynamic(pysdm, case, host_rng):
     """`pysdm_b200.FusedCoalescence` (PySDM's Coalescence with step() on the one-launch fused
     kernel) inside the unmodified PySDM orchestration.  host_rng=True: against the reference's
@@ -175,14 +176,19 @@ def test_fused_coalescence_dynamic(pysdm, case, host_rng):
         np.testing.assert_array_equal(a["multiplicity"], b["multiplicity"])
         assert_same_f64(a["attributes"], b["attributes"], f"step {step}: attributes")
         assert_same_f64(a["gamma"], b["gamma"], f"step {step}: gamma")
-        for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate"):
+        for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate",
+                  "stats_n_substep"):
             np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
+        assert_same_f64(a["stats_dt_min"], b["stats_dt_min"], f"step {step}: stats_dt_min")
         # derived attributes are recomputed from what the fused step wrote
         np.testing.assert_array_equal(sut.attributes["volume"].to_ndarray(),
                                       ref.attributes["volume"].to_ndarray())
     dyn = sut.dynamics["Collision"]
-    expected = 0 if case == "global" else 8 * c["kw"].get("substeps", 1)
-    assert dyn.n_fused_steps == expected
+    if c["kw"].get("adaptive"):  # one fused launch per sub-step of the adaptive loop
+        assert dyn.n_fused_steps >= int(snapshot(ref)["stats_n_substep"].max()) > 8
+    else:
+        expected = 0 if case == "global" else 8 * c["kw"].get("substeps", 1)
+        assert dyn.n_fused_steps == expected
     assert int(snapshot(ref)["coalescence_rate"].sum()) > 0
 
 

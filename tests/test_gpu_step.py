@@ -94,6 +94,20 @@ CASES = {
     "big_cells": dict(seed=3, n_cell=5, mean=3000, n_attr=1, dv=2e-5, steps=3),
     "substeps": dict(seed=4, n_cell=64, mean=40, n_attr=2, dv=1e-7, steps=4, substeps=3),
     "one_cell": dict(seed=5, n_cell=1, mean=5000, n_attr=1, dv=2e-6, steps=3),
+    # adaptive time step (one fused launch per sub-step): ragged cells so that the re-sorted
+    # cell_idx shifts the pair parity (quirk A2) and `normalize` picks other cells' factors (A1)
+    "adaptive_ragged": dict(seed=6, n_cell=300, mean=40, n_attr=3, dv=1e-8, steps=4,
+                            adaptive=True, dt_coal_range=(0.01, 1.0)),
+    "adaptive_optrand": dict(seed=7, n_cell=120, mean=60, n_attr=2, dv=2e-8, steps=4,
+                             adaptive=True, dt_coal_range=(0.05, 1.0), optimized_random=True),
+    # small multiplicities: SDs are removed inside the sub-step loop, the re-sort by cell then
+    # uses the dt_left-sorted cell_idx (ranks are no longer cell ids)
+    "adaptive_removals": dict(seed=8, n_cell=200, mean=50, n_attr=1, dv=1e-8, steps=5,
+                              adaptive=True, dt_coal_range=(0.02, 1.0), max_mult=2),
+    "adaptive_big_cells": dict(seed=9, n_cell=6, mean=2500, n_attr=1, dv=3e-7, steps=3,
+                               adaptive=True, dt_coal_range=(0.05, 1.0), max_mult=3),
+    "adaptive_dt_min": dict(seed=10, n_cell=50, mean=30, n_attr=1, dv=2e-10, steps=2,
+                            adaptive=True, dt_coal_range=(0.25, 1.0)),
 }
 
 
@@ -103,10 +117,11 @@ def test_against_oracle(case, fused):
     c = dict(CASES[case])
     steps, dv = c.pop("steps"), c.pop("dv")
     substeps = c.pop("substeps", 1)
+    extra = {k: c.pop(k) for k in ("adaptive", "dt_coal_range", "optimized_random") if k in c}
     pop = ragged_population(**c)
     if case == "one_cell":
         pop["cell_id"] = np.zeros_like(pop["cell_id"])
-    common = dict(dt=1.0, dv=dv, seed=100 + c["seed"], substeps=substeps)
+    common = dict(dt=1.0, dv=dv, seed=100 + c["seed"], substeps=substeps, **extra)
     ora = OracleCollision(kernel=OGolovin(GOLOVIN_B), **pop, **common)
     dev = device_sim(kernel=device_kernel(b=GOLOVIN_B), host_rng=True, fused=fused, **pop,
                      **common)
@@ -115,7 +130,12 @@ def test_against_oracle(case, fused):
         dev()
         compare_states(dev, ora, f"{case} step {step}")
     assert ora.coalescence_rate.sum() > 0, "test population never collided"
-    if fused:
+    if extra.get("adaptive"):
+        assert ora.stats_n_substep.max() > steps, "the time step was never cut"
+        np.testing.assert_array_equal(dev.host("dt_left"), ora.dt_left)
+        if fused:
+            assert dev.n_fused_steps >= ora.stats_n_substep.max()
+    elif fused:
         assert dev.n_fused_steps == steps * substeps
 
 

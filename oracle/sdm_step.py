@@ -43,6 +43,30 @@ class Golovin:
         output *= self.b
 
 
+class ConstantK:
+    """collision_kernels/constantK.py:11-12"""
+
+    def __init__(self, a):
+        self.a = a
+
+    def __call__(self, box, output, flag):
+        output.fill(self.a)
+
+
+class Linear:
+    """collision_kernels/linear.py:12-15 as intended (the reference spells the pair sum
+    `output.sum_pair`, which PairwiseStorage does not have -- its own TODO #744; Golovin,
+    golovin.py:14-16, is the same sequence without the `+= a`)"""
+
+    def __init__(self, a, b):
+        self.a, self.b = a, b
+
+    def __call__(self, box, output, flag):
+        box.be.pair_op("sum", output, box.volume(), flag, box.idx, box.length)
+        output *= self.b
+        output += self.a
+
+
 class OracleCollision:  # pylint: disable=too-many-instance-attributes
     """state + time step of `Coalescence(collision_kernel=...)` in a Box or on a mesh"""
 

@@ -301,15 +301,38 @@ __global__ void k_f64_sort_keys(const double *__restrict__ attr, u64 *__restrict
     vals[i] = i;
 }
 
-// Small arrays (the per-cell keys of one GPU's slab: a few 10^4 cells): the whole sort --
-// key construction, 8 stable passes, reversed output -- in ONE launch of one 1024-thread CTA.
-// The multi-kernel path above costs 5 launches per pass, ~30 us each way for 32768 keys, and
-// was a third of the GPU time of an adaptive sub-step (profiles/r1_config3_launches).
+// Small arrays (the per-cell keys of one GPU's slab: a few 10^4 cells): the whole sort in ONE
+// launch of one 1024-thread CTA.  The keys of the adaptive loop (`dt_left` per cell,
+// collision.py:181) are far from arbitrary: all equal before the first sub-step, and from the
+// second one on most cells are finished (dt_left == 0).  So:
+//   1. the elements holding the MINIMAL key need no sorting -- they come last, in descending
+//      index order (stable ascending argsort, reversed); the others are compacted (stable);
+//   2. the compacted keys go through stable 8-bit LSD passes, but only over the digits in which
+//      they actually differ (OR / AND of the keys), the last pass writing the reversed order.
+// All keys equal: no pass at all.  General keys: the 8 passes of before on n - (count of min).
 // Per pass: warp-private digit histograms in shared memory (warp w owns a contiguous chunk),
 // exclusive scan over (digit-major, warp-minor), in-order replay of every chunk -- the same
 // stable construction as radix_histogram / radix_scatter.
 constexpr int kSmallSortThreads = 1024, kSmallSortWarps = kSmallSortThreads / 32;
 constexpr i64 kSmallSortMax = 65536;
+
+__device__ __forceinline__ u64 f64_sort_key(double v)
+{
+    if (v == 0.0) v = 0.0;  // -0.0 and +0.0 are ties for numpy
+    const u64 b = (u64)__double_as_longlong(v);
+    if (v != v) return ~(u64)0;  // every NaN last, like numpy
+    return (b >> 63) ? ~b : (b | ((u64)1 << 63));
+}
+
+__device__ __forceinline__ u64 warp_reduce_u64(u64 v, int op)  // 0 min, 1 or, 2 and
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const u64 t = __shfl_xor_sync(0xffffffffu, v, o);
+        v = op == 0 ? (t < v ? t : v) : (op == 1 ? (v | t) : (v & t));
+    }
+    return v;
+}
 
 __global__ void __launch_bounds__(kSmallSortThreads)
     k_sort_by_key_small(const double *__restrict__ attr, u64 *ka, i64 *va, u64 *kb, i64 *vb,
@@ -317,24 +340,95 @@ __global__ void __launch_bounds__(kSmallSortThreads)
 {
     __shared__ u32 hist[kRadixBins][kSmallSortWarps + 1];  // [digit][warp], padded
     __shared__ u32 warp_sums[kSmallSortWarps];
+    __shared__ unsigned long long s_min, s_or, s_and;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lt = (1u << lane) - 1u;
-    for (int i = tid; i < n; i += kSmallSortThreads) {  // k_f64_sort_keys
-        double v = attr[i];
-        if (v == 0.0) v = 0.0;  // -0.0 and +0.0 are ties for numpy
-        u64 b = (u64)__double_as_longlong(v);
-        if (v != v)
-            b = ~(u64)0;
-        else
-            b = (b >> 63) ? ~b : (b | ((u64)1 << 63));
-        ka[i] = b;
-        va[i] = i;
+    if (tid == 0) {
+        s_min = ~0ull;
+        s_or = 0ull;
+        s_and = ~0ull;
     }
-    // contiguous chunk of warp w: [w * chunk, (w + 1) * chunk), chunk a multiple of 32
-    const int chunk = ((n + kSmallSortWarps - 1) / kSmallSortWarps + 31) / 32 * 32;
-    const int begin = warp * chunk, end = begin + chunk < n ? begin + chunk : n;
-    for (int p = 0; p < 8; ++p) {
-        const int shift = 8 * p;
+    __syncthreads();
+    {  // minimal key
+        u64 m = ~(u64)0;
+        for (int i = tid; i < n; i += kSmallSortThreads) {
+            const u64 k = f64_sort_key(attr[i]);
+            m = k < m ? k : m;
+        }
+        m = warp_reduce_u64(m, 0);
+        if (lane == 0) atomicMin(&s_min, (unsigned long long)m);
+    }
+    __syncthreads();
+    const u64 kmin = s_min;
+    // stable compaction of the elements above the minimum: warp w owns a contiguous chunk
+    const int chunk0 = ((n + kSmallSortWarps - 1) / kSmallSortWarps + 31) / 32 * 32;
+    const int begin0 = warp * chunk0, end0 = begin0 + chunk0 < n ? begin0 + chunk0 : n;
+    {
+        u32 cnt = 0;
+        u64 o = 0, a = ~(u64)0;
+        for (int i = begin0 + lane; i < end0; i += 32) {
+            const u64 k = f64_sort_key(attr[i]);
+            if (k != kmin) {
+                ++cnt;
+                o |= k;
+                a &= k;
+            }
+        }
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        o = warp_reduce_u64(o, 1);
+        a = warp_reduce_u64(a, 2);
+        if (lane == 0) {
+            warp_sums[warp] = cnt;
+            atomicOr(&s_or, (unsigned long long)o);
+            atomicAnd(&s_and, (unsigned long long)a);
+        }
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const u32 w = warp_sums[lane];
+        u32 winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const u32 t = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += t;
+        }
+        warp_sums[lane] = winc - w;
+        if (lane == 31) hist[0][0] = winc;  // total
+    }
+    __syncthreads();
+    const int n_act = (int)hist[0][0];
+    const u64 differ = n_act > 1 ? (s_or & ~s_and) : 0;  // bits in which the compacted keys differ
+    int passes[8], n_pass = 0;
+    for (int p = 0; p < 8; ++p)
+        if ((differ >> (8 * p)) & 0xffu) passes[n_pass++] = p;
+    {
+        u32 off = warp_sums[warp];  // compacted elements before my chunk
+        for (int i0 = begin0; i0 < end0; i0 += 32) {
+            const int i = i0 + lane;
+            const bool in = i < end0;
+            const u64 k = in ? f64_sort_key(attr[i]) : kmin;
+            const bool act = in && k != kmin;
+            const unsigned m = __ballot_sync(0xffffffffu, act);
+            const u32 pos = off + __popc(m & lt);
+            if (act) {
+                if (n_pass == 0) {
+                    idx[n_act - 1 - (int)pos] = i;  // already in order: reversed
+                } else {
+                    ka[pos] = k;
+                    va[pos] = i;
+                }
+            } else if (in) {
+                idx[n - 1 - (i - (int)pos)] = i;  // i - pos minimal-key elements precede i
+            }
+            off += __popc(m);
+        }
+    }
+    __syncthreads();  // orders the global writes above before the reads of the passes
+    const int chunk = ((n_act + kSmallSortWarps - 1) / kSmallSortWarps + 31) / 32 * 32;
+    const int begin = warp * chunk < n_act ? warp * chunk : n_act;
+    const int end = begin + chunk < n_act ? begin + chunk : n_act;
+    for (int q = 0; q < n_pass; ++q) {
+        const int shift = 8 * passes[q];
         for (int e = tid; e < kRadixBins * (kSmallSortWarps + 1); e += kSmallSortThreads)
             (&hist[0][0])[e] = 0;
         __syncthreads();  // also orders the previous pass's global writes before these reads
@@ -382,7 +476,7 @@ __global__ void __launch_bounds__(kSmallSortThreads)
         }
         __syncthreads();
         // in-order replay of my chunk; hist[d][warp] is the running output offset
-        const bool last = p == 7;
+        const bool last = q == n_pass - 1;
         for (int i0 = begin; i0 < end; i0 += 32) {
             const int i = i0 + lane;
             const bool active = i < end;
@@ -397,7 +491,7 @@ __global__ void __launch_bounds__(kSmallSortThreads)
             __syncwarp();
             if (active) {
                 if (last) {
-                    idx[n - 1 - (int)pos] = val;  // [::-1]
+                    idx[n_act - 1 - (int)pos] = val;  // [::-1]
                 } else {
                     kb[pos] = key;
                     vb[pos] = val;

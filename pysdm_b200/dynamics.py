@@ -51,6 +51,7 @@ _KERNELS = {"Golovin": lambda k: (0.0, k.b), "ConstantK": lambda k: (k.a, 0.0),
 def make_fused_coalescence():
     """builds the class lazily: importing pysdm_b200 must not need PySDM"""
     from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics.collisions.collision_kernels.impl.parameterized import Parameterized  # pylint: disable=import-outside-toplevel
 
     from .backend import B200  # pylint: disable=import-outside-toplevel
 
@@ -82,6 +83,8 @@ def make_fused_coalescence():
             """(kernel name, a, b, caretaker of the current sort) or None"""
             part = self.particulator
             name = type(self.collision_kernel).__name__
+            if isinstance(self.collision_kernel, Parameterized):
+                name = "Hydrodynamic"  # (also `Electric`: Berry's form with other parameters)
             if (not isinstance(part.backend, B200) or self.enable_breakup
                     or self.croupier != "local" or name not in _KERNELS
                     or part.n_sd >= 2 ** 32

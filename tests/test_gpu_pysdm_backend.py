@@ -483,3 +483,209 @@ def test_fused_coalescence_geometric(pysdm, kernel, grid, host_rng):
             np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
     assert sut.dynamics["Collision"].n_fused_steps == 6
     assert int(snapshot(ref)["coalescence_rate"].sum()) > 0
+
+
+# ---- the remaining collision kernels through the stock dynamic -------------------
+def _kernel(name):
+    # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics.collisions.collision_kernels import (ConstantK, Electric, Linear,
+                                                             SimpleGeometric)
+
+    return {"ConstantK": lambda: ConstantK(a=2e-11), "Linear": lambda: Linear(a=1e-10, b=1.5e3),
+            "Electric": Electric, "SimpleGeometric": lambda: SimpleGeometric(C=3e5)}[name]()
+
+
+@pytest.mark.parametrize("fused", (False, True))
+@pytest.mark.parametrize("kernel", ("ConstantK", "Electric", "SimpleGeometric", "Linear"))
+def test_other_collision_kernels_equal_numba(pysdm, kernel, fused):
+    """collision_kernels/{constantK,electric,simple_geometric,linear}.py through the unmodified
+    orchestration: B200 (stock `Coalescence`, and `FusedCoalescence`, which covers ConstantK and
+    -- as a Parameterized kernel -- Electric) against the Numba backend, same uniforms.
+    The reference's `Linear` is broken upstream (`output.sum_pair` does not exist on
+    PairwiseStorage, linear.py:13; its own header says TODO #744): both backends must fail the
+    same way."""
+    from PySDM import Builder, Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+    from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
+    from PySDM.impl.mesh import Mesh  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200, FusedCoalescence  # pylint: disable=import-outside-toplevel
+
+    n_sd, grid = 4096, (4, 4)
+    rng = np.random.default_rng(23)
+    attributes = {
+        "multiplicity": rng.integers(200, 4000, n_sd).astype(np.int64),
+        "volume": 4 / 3 * np.pi * (rng.exponential(12e-6, n_sd) + 2e-6) ** 3,
+        "cell id": rng.integers(0, 16, n_sd).astype(np.int64),
+    }
+
+    def make(backend, dynamic):
+        dv = {"ConstantK": 1e-5, "Electric": 0.04}.get(kernel, 0.004)
+        env = Box(dv=dv, dt=10.0)
+        env.mesh = Mesh(grid, size=grid, dv=dv)
+        builder = Builder(n_sd=n_sd, backend=backend, environment=env)
+        builder.add_dynamic(dynamic(collision_kernel=_kernel(kernel), adaptive=False))
+        return builder.build(attributes={k: v.copy() for k, v in attributes.items()}, products=())
+
+    fkw = dict(fastmath=False, seed=57)
+    ref = make(CPU(Formulae(**fkw)), Coalescence)
+    sut = make(B200(Formulae(**fkw), host_rng=True), FusedCoalescence if fused else Coalescence)
+    if kernel == "Linear":
+        with pytest.raises(AttributeError, match="sum_pair"):
+            ref.run(1)
+        if fused:  # the fused step evaluates the kernel itself (sum, *= b, += a; pinned on the
+            # oracle in test_gpu_step.py::test_other_kernels_against_oracle) and does run
+            sut.run(5)
+            assert sut.dynamics["Collision"].n_fused_steps == 5
+            assert int(snapshot(sut)["coalescence_rate"].sum()) > 0
+        else:
+            with pytest.raises(AttributeError, match="sum_pair"):
+                sut.run(1)
+        return
+    for step in range(5):
+        ref.run(1)
+        sut.run(1)
+        a, b = snapshot(sut), snapshot(ref)
+        n = b["length"]
+        assert a["length"] == n, f"step {step}: length"
+        np.testing.assert_array_equal(a["idx"][:n], b["idx"][:n], f"step {step}: idx")
+        np.testing.assert_array_equal(a["flag"][:n], b["flag"][:n], f"step {step}: flag")
+        flips = int((a["gamma"] != b["gamma"]).sum())
+        assert flips == 0, f"step {step}: {flips} gamma values differ (integer-boundary flips)"
+        np.testing.assert_array_equal(a["multiplicity"], b["multiplicity"], f"step {step}")
+        np.testing.assert_allclose(a["attributes"], b["attributes"], rtol=1e-12, atol=0)
+        for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate"):
+            np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
+    assert int(snapshot(ref)["coalescence_rate"].sum()) > 0
+    if fused:
+        expected = 5 if kernel in ("ConstantK", "Electric") else 0
+        assert sut.dynamics["Collision"].n_fused_steps == expected
+
+
+# ---- BASELINE.json configs at (or in the kind of) their stated sizes ------------------------------
+def _compare_runs(ref, suts, steps, *, breakup=False, fused_expected=()):
+    events = 0
+    for step in range(steps):
+        ref.run(1)
+        b = snapshot(ref)
+        n = b["length"]
+        for name, sut in suts.items():
+            sut.run(1)
+            a = snapshot(sut)
+            what = f"{name} step {step}"
+            assert a["length"] == n, f"{what}: length"
+            np.testing.assert_array_equal(a["idx"][:n], b["idx"][:n], f"{what}: idx")
+            np.testing.assert_array_equal(a["flag"][:n], b["flag"][:n], f"{what}: flag")
+            flips = int((a["gamma"] != b["gamma"]).sum())
+            print(f"{what}: gamma integer-boundary flips = {flips} of {a['gamma'].size}")
+            assert flips == 0, f"{what}: {flips} gamma values differ (integer-boundary flips)"
+            np.testing.assert_array_equal(a["multiplicity"], b["multiplicity"], what)
+            np.testing.assert_allclose(a["attributes"], b["attributes"], rtol=1e-12, atol=0,
+                                       err_msg=what)
+            for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate",
+                      "stats_n_substep"):
+                np.testing.assert_array_equal(a[k], b[k], f"{what}: {k}")
+            assert_same_f64(a["stats_dt_min"], b["stats_dt_min"], f"{what}: stats_dt_min")
+            if breakup:
+                for k in ("breakup_rate", "breakup_rate_deficit"):
+                    np.testing.assert_array_equal(
+                        getattr(sut.dynamics["Collision"], k).to_ndarray(),
+                        getattr(ref.dynamics["Collision"], k).to_ndarray(), f"{what}: {k}")
+        events += int(b["coalescence_rate"].sum())
+    assert events > 0
+    for name in fused_expected:
+        assert suts[name].dynamics["Collision"].n_fused_steps > 0, name
+
+
+def test_config4_in_kind(pysdm):
+    """BASELINE configs[3] (Sc-rain, Arabas et al. 2015) in kind: a 2-D mesh of 32 x 32 cells
+    with 128 super-droplets each, `Coalescence(Geometric(1), adaptive=True,
+    optimized_random=True)` (Morrison_and_Grabowski_2007/common.py:30-35), A = 3 extensive
+    attributes ("dry volume", "kappa times dry volume" next to the water mass,
+    environments/kinematic_2d.py:63-64,84), dt = 5 s, dv of one 1.5 km / 512 cell: Numba
+    backend vs B200 with the stock dynamic and with `FusedCoalescence` (fused adaptive
+    sub-steps), same uniforms"""
+    from PySDM import Builder, Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics.collisions.collision_kernels import Geometric  # pylint: disable=import-outside-toplevel
+    from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
+    from PySDM.impl.mesh import Mesh  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200, FusedCoalescence  # pylint: disable=import-outside-toplevel
+
+    grid, per_cell = (32, 32), 128
+    n_cell = grid[0] * grid[1]
+    n_sd = n_cell * per_cell
+    dv = (1500 / 512) ** 2
+    rng = np.random.default_rng(2015)
+    volume = 4 / 3 * np.pi * (10e-6 * np.exp(0.47 * rng.standard_normal(n_sd))) ** 3
+    volume[rng.random(n_sd) < 0.01] *= 60.0  # a few drizzle drops: cells that need sub-steps
+    attributes = {
+        "volume": volume, "cell id": np.arange(n_sd, dtype=np.int64) // per_cell,
+        "multiplicity": rng.integers(1, 2 * int(100e6 * dv / per_cell), n_sd).astype(np.int64),
+        "dry volume": volume * 1e-3, "kappa times dry volume": volume * 0.6e-3}
+
+    def make(backend, dynamic):
+        env = Box(dv=dv, dt=5.0)
+        env.mesh = Mesh(grid, size=grid, dv=dv)
+        builder = Builder(n_sd=n_sd, backend=backend, environment=env)
+        builder.add_dynamic(dynamic(collision_kernel=Geometric(collection_efficiency=1),
+                                    adaptive=True, optimized_random=True))
+        builder.request_attribute("dry volume")
+        builder.request_attribute("kappa times dry volume")
+        return builder.build(attributes={k: v.copy() for k, v in attributes.items()}, products=())
+
+    fkw = dict(fastmath=False, seed=15)
+    ref = make(CPU(Formulae(**fkw)), Coalescence)
+    assert len(ref.attributes.get_extensive_attribute_keys()) == 3
+    suts = {"stock": make(B200(Formulae(**fkw), host_rng=True), Coalescence),
+            "fused": make(B200(Formulae(**fkw), host_rng=True), FusedCoalescence)}
+    _compare_runs(ref, suts, 4, fused_expected=("fused",))
+    assert int(snapshot(ref)["stats_n_substep"].max()) > 4, "no cell needed a sub-step"
+
+
+def test_config2_full_size(pysdm):
+    """BASELINE configs[1] at its size: Berry 1967 box, 2^20 super-droplets in one cell,
+    `Coalescence(Hydrodynamic(), adaptive=True, dt_coal_range=(0.1, 100))`, dt = 10 s, dv = 10 m^3
+    (Berry_1967/settings.py:25-38), B200 vs Numba, same uniforms, 3 steps"""
+    from PySDM import Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200  # pylint: disable=import-outside-toplevel
+
+    n_sd = 1 << 20
+    rng = np.random.default_rng(1967)
+    volume = rng.exponential(4 / 3 * np.pi * 10e-6 ** 3, n_sd)
+    attributes = {"volume": volume,
+                  "multiplicity": np.full(n_sd, int(239e6 * 10 / n_sd), dtype=np.int64)}
+    fkw = dict(fastmath=False, seed=67)
+    common = dict(n_sd=n_sd, dv=10.0, dt=10.0, attributes=attributes,
+                  dynamic=_dynamics("hydrodynamic_adaptive"))
+    ref = build_physics(pysdm, CPU(Formulae(**fkw)), **common)
+    sut = build_physics(pysdm, B200(Formulae(**fkw), host_rng=True), **common)
+    _compare_runs(ref, {"b200": sut}, 3)
+
+
+def test_config3_full_size(pysdm):
+    """BASELINE configs[2] at its size: de Jong et al. breakup box, 2^22 super-droplets,
+    `Collision(Geometric(), Straub2010Ec(), ConstEb(1), Straub2010Nf(...), adaptive=True)`,
+    dt = 1 s, dv = 10^6 m^3 (deJong_Mackay_et_al_2023/settings_0D.py:27-52), B200 vs Numba,
+    same uniforms, 2 steps"""
+    from PySDM import Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200  # pylint: disable=import-outside-toplevel
+
+    n_sd = 1 << 22
+    rng = np.random.default_rng(2023)
+    volume = rng.exponential(4 / 3 * np.pi * 0.2e-3 ** 3, n_sd)
+    attributes = {"volume": volume,
+                  "multiplicity": np.full(n_sd, max(1, int(1e3 * 1e6 / n_sd)), dtype=np.int64)}
+    fkw = dict(fastmath=False, seed=23, fragmentation_function="Straub2010Nf")
+    common = dict(n_sd=n_sd, dv=1e6, dt=1.0, attributes=attributes,
+                  dynamic=_dynamics("breakup_straub"))
+    ref = build_physics(pysdm, CPU(Formulae(**fkw)), **common)
+    sut = build_physics(pysdm, B200(Formulae(**fkw), host_rng=True), **common)
+    _compare_runs(ref, {"b200": sut}, 2, breakup=True)

@@ -139,18 +139,24 @@ def test_against_oracle(case, fused):
         assert dev.n_fused_steps == steps * substeps
 
 
+@pytest.mark.parametrize("fused", (True, False))
 @pytest.mark.parametrize("kernel", ("ConstantK", "Linear"))
-def test_fused_equals_methods_other_kernels(kernel):
-    """fused vs method-level CUDA path (itself pinned by the tests above)"""
+def test_other_kernels_against_oracle(kernel, fused):
+    """collision_kernels/constantK.py:11-12 and linear.py:12-15, fused and method-level, against
+    the oracle's restatement of the same operation sequences (`fill`; `sum_pair`, `*=`, `+=`)"""
+    from oracle import sdm_step  # pylint: disable=import-outside-toplevel
+
     pop = ragged_population(seed=7, n_cell=200, mean=60, n_attr=2)
     kw = {"ConstantK": {"a": 3e-4}, "Linear": {"a": 1e-4, "b": GOLOVIN_B}}[kernel]
-    sims = [device_sim(kernel=device_kernel(kernel, **kw), dt=1.0, dv=1e-3, seed=3, host_rng=True,
-                       fused=f, **pop) for f in (True, False)]
+    common = dict(dt=1.0, dv=1e-3, seed=3, **pop)
+    ora = OracleCollision(kernel=getattr(sdm_step, kernel)(**kw), **common)
+    dev = device_sim(kernel=device_kernel(kernel, **kw), host_rng=True, fused=fused, **common)
     for step in range(4):
-        for s in sims:
-            s()
-        compare_states(sims[0], _Host(sims[1]), f"{kernel} step {step}")
-    assert sims[0].host("coalescence_rate").sum() > 0
+        ora()
+        dev()
+        compare_states(dev, ora, f"{kernel} step {step}")
+    assert ora.coalescence_rate.sum() > 0
+    assert dev.n_fused_steps == (4 if fused else 0)
 
 
 def test_fused_philox_equals_methods_philox():
@@ -223,9 +229,36 @@ def test_host_step_stripes_equal_separate_runs():
     assert rate.sum() > 0 and host.h2d_bytes == mult.size * 8 * 4
 
 
+@pytest.mark.parametrize("adaptive", (False, True))
+def test_full_size_fused_equals_oracle(adaptive):
+    """BASELINE.json's headline size -- 2^24 super-droplets in 2^17 cells of 128, the bench.py
+    workload (configs[4]) -- fused step against the CPU oracle, same uniforms (the oracle's
+    PCG64 stream replayed on the device), two time steps, everything bit for bit; also with the
+    adaptive time step (one fused launch per sub-step)"""
+    n_sd, per_cell = 1 << 24, 128
+    rng = np.random.default_rng(4321)
+    pop = {"multiplicity": rng.integers(1, 5, n_sd).astype(np.int64),
+           "water_mass": rng.exponential(1000 * 4 / 3 * np.pi * 30.531e-6 ** 3, n_sd),
+           "cell_id": np.arange(n_sd, dtype=np.int64) // per_cell, "n_cell": n_sd // per_cell}
+    common = dict(dt=1.0, dv=2e-7 if not adaptive else 4e-8, seed=7)
+    if adaptive:
+        common.update(adaptive=True, dt_coal_range=(0.25, 1.0))
+    ora = OracleCollision(kernel=OGolovin(GOLOVIN_B), **pop, **common)
+    dev = device_sim(kernel=device_kernel(b=GOLOVIN_B), host_rng=True, fused=True, **pop, **common)
+    for step in range(2):
+        ora()
+        dev()
+        compare_states(dev, ora, f"2^24 step {step}")
+    assert ora.coalescence_rate.sum() > 0
+    assert dev.n_fused_steps >= (int(ora.stats_n_substep.max()) if adaptive else 2)
+    if adaptive:
+        assert ora.stats_n_substep.max() > 2, "the time step was never cut"
+
+
 def test_full_size_properties_and_fused_equals_methods():
     """BASELINE.json's headline size (2^24 super-droplets, 2^17 cells of 128, the bench.py
-    workload), where the oracle would take minutes: the fused step must equal the method-level
+    workload) with the device Philox stream (which the oracle cannot replay; the test above
+    pins the same kernel on the oracle's stream): the fused step must equal the method-level
     kernels bit for bit (same Philox stream), and the size-independent invariants of a
     coalescence step must hold: idx stays a permutation, every cell keeps its droplets, the
     number of pairs is sum(n_c // 2), the drop in total multiplicity equals the coalescence

@@ -213,6 +213,34 @@ def test_sort_by_key_sizes(be, n):
     np.testing.assert_array_equal(out, np.argsort(keys, kind="stable")[::-1])
 
 
+@pytest.mark.parametrize("shape", ("all_equal", "mostly_zero", "two_values", "low_bytes_differ",
+                                   "one_nonzero", "all_distinct"))
+@pytest.mark.parametrize("n", (7, 4097, 32768))
+def test_sort_by_key_adaptive_shapes(be, n, shape):
+    """the key sets the adaptive loop produces (collision.py:181, `dt_left` per cell): all equal
+    before the first sub-step, mostly 0 afterwards -- the one-CTA sort treats the minimal key and
+    constant digits specially"""
+    rng = np.random.default_rng(n + len(shape))
+    if shape == "all_equal":
+        keys = np.full(n, 5.0)
+    elif shape == "mostly_zero":
+        keys = np.zeros(n)
+        some = rng.random(n) < 0.03
+        keys[some] = 5.0 - rng.random(int(some.sum())) * 4.9
+    elif shape == "two_values":
+        keys = rng.choice([0.0, 5.0], n)
+    elif shape == "low_bytes_differ":
+        keys = (1.0 + rng.integers(0, 1 << 14, n) * 2.0 ** -52)
+    elif shape == "one_nonzero":
+        keys = np.zeros(n)
+        keys[n // 3] = 0.25
+    else:
+        keys = rng.random(n)
+    out = np.full(n, -1, np.int64)
+    be.sort_by_key(out, keys)
+    np.testing.assert_array_equal(out, np.argsort(keys, kind="stable")[::-1])
+
+
 # ---- whole time steps ---------------------------------------------------------------------
 def make_oracle_from_scenario(s, name, be=orc):
     kw = dict(SCENARIO_KW[name])

@@ -235,6 +235,20 @@ typedef struct pysdm_b200_fused_args {
     const int64_t *length_dev;   /* [1] or NULL: working length read on the device instead of
                                     `length` (the adaptive_end[0] of the previous sub-step); a
                                     launch that finds 0 there does nothing */
+    /* ---- dependent attributes (kernels 3, 4): the orchestration derives volume, radius and fall
+     * velocity from the water mass (attributes/physics/{volume,radius,terminal_velocity}.py) and
+     * recomputes all of them after every step; with dep_radius != NULL the launch instead
+     * refreshes them for exactly the super-droplets a coalescence changed -- same operation
+     * sequence, so the arrays equal a full recomputation bit for bit */
+    double *dep_volume;          /* [n_sd] or NULL ("volume" attribute) */
+    double *dep_radius;          /* [n_sd] or NULL; normally == radius */
+    double *dep_velocity;        /* [n_sd] or NULL; normally == fall_velocity */
+    const double *dep_table_b, *dep_table_c; /* Gunn-Kinzer interpolation tables (`a`, `b` of
+                                    dynamics/terminal_velocity/gunn_and_kinzer.py:108-125) */
+    double dep_radius_scale, dep_radius_exponent; /* 1 / PI_4_3 and 1 / 3 as the host computes them */
+    double dep_table_factor, dep_radius_max;      /* Interpolation.factor, .maximum_radius */
+    int64_t *dep_status;         /* [1]: set to 1 if a refreshed radius exceeds dep_radius_max (the
+                                    reference raises ValueError at the next recalculation) */
 } pysdm_b200_fused_args;
 
 int64_t pysdm_b200_fused_max_cell_size(void);
@@ -249,6 +263,14 @@ int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *host_args, void
 /* out[in[c]] = c for c < n: the rank -> cell map (`rank_to_cell` above) of the cell -> rank map
  * `cell_idx` a sort by cell has just used (collisions_methods.py:692-697 consume it that way) */
 int pysdm_b200_invert_index(int64_t *out, const int64_t *in, int64_t n, void *stream);
+/* volume, radius, fall velocity of every super-droplet from the water mass in one pass
+ * (volume_of_water_mass, Radius.recalculate = product + `**=`, Gunn-Kinzer `interpolation`; the
+ * five-launch chain of attributes/physics/{volume,radius,terminal_velocity}.py); any output may be
+ * NULL.  status[0] is set to 1 if a radius exceeds radius_max (no velocity is written for it). */
+int pysdm_b200_dependent_attributes(const double *mass, int64_t n, double rho_w, double radius_scale,
+                                    double radius_exponent, double table_factor, double radius_max,
+                                    const double *table_b, const double *table_c, double *volume,
+                                    double *radius, double *velocity, int64_t *status, void *stream);
 
 /* ---- terminal velocities: methods/terminal_velocity_methods.py ----------------------- */
 

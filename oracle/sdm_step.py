@@ -67,6 +67,37 @@ class Linear:
         output += self.a
 
 
+class Geometric:
+    """collision_kernels/geometric.py:15-22 on the attributes the orchestration derives from the
+    water mass before the kernel reads them: volume (attributes/physics/volume.py:17), radius
+    (radius.py:15-17: product with 1 / PI_4_3, then `**= 1/3`), fall velocity (Gunn-Kinzer
+    `interpolation`, dynamics/terminal_velocity/gunn_and_kinzer.py:128-133); `table` = (a, b,
+    factor, maximum_radius) of the reference's GunnKinzer1949 object"""
+    PI = 3.141592653589793
+    PI_4_3 = PI * 4 / 3
+
+    def __init__(self, collection_efficiency, table):
+        self.collection_efficiency = collection_efficiency
+        self.table = table
+        self.radius = self.velocity = self.pair_tmp = None
+
+    def __call__(self, box, output, flag):
+        be = box.be
+        if self.radius is None:
+            self.radius, self.velocity = np.empty(box.n_sd), np.empty(box.n_sd)
+            self.pair_tmp = np.empty(box.n_sd // 2)
+        be.product_scalar(self.radius, box.volume(), 1 / self.PI_4_3)
+        be.power(self.radius, 1 / 3)
+        a, b, factor, r_max = self.table
+        assert not self.radius.max() > r_max
+        be.interpolation(self.velocity, self.radius, factor, a, b)
+        be.pair_op("sum", output, self.radius, flag, box.idx, box.length)
+        be.power(output, 2)
+        output *= self.PI * self.collection_efficiency
+        be.pair_op("distance", self.pair_tmp, self.velocity, flag, box.idx, box.length)
+        output *= self.pair_tmp
+
+
 class OracleCollision:  # pylint: disable=too-many-instance-attributes
     """state + time step of `Coalescence(collision_kernel=...)` in a Box or on a mesh"""
 

@@ -20,8 +20,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "oracle", "refshims"))
-_REF = next((p for p in (os.path.join(ROOT, "baseline", "_ref"), "/root/reference")
-             if os.path.isdir(os.path.join(p, "PySDM"))), None)
+_REF = os.path.join(ROOT, "baseline", "_ref")  # the unmodified reference (travels to the GPU box)
+if not os.path.isdir(os.path.join(_REF, "PySDM")):
+    raise ImportError("no PySDM install under baseline/_ref")
 sys.path.insert(1, _REF)
 os.environ.setdefault("CI", "1")
 np.NaN = np.nan
@@ -67,8 +68,9 @@ SETUP = {
             dv=1e6, r0=0.2e-3, norm=1e3 * 1e6,
             fkw={"fragmentation_function": "Straub2010Nf"}),
     # per-GPU share of configs[3]: 32768 cells of 128 SDs, dv of one cell of the 1.5 km / 512 grid
-    3: dict(name="Sc-rain collision step, Geometric + adaptive, 2^22 SDs in 32768 cells", log2=22,
-            dt=5.0, dv=(1500 / 512) ** 2, r0=10e-6, norm=None, fkw={}, sd_per_cell=128),
+    3: dict(name="Sc-rain collision step, Geometric + adaptive + optimized_random, A=3, "
+                 "2^22 SDs in 32768 cells", log2=22,
+            dt=5.0, dv=(1500 / 512) ** 2, r0=10e-6, norm=None, fkw={}, sd_per_cell=128, n_attr=3),
     4: dict(name="Golovin multi-cell coalescence, 2^24 SDs in 2^17 cells (bench.py workload)",
             log2=24, dt=1.0, dv=1.0, r0=30.531e-6, norm=None, fkw={}, sd_per_cell=128,
             multiplicity=2 ** 20),
@@ -81,7 +83,51 @@ SETUP = {
 }
 
 
-def run(config, backend_name, steps, log2=None):
+BYTES_PER_SD = {0: 73, 1: 73, 2: 81, 3: 105, 4: 73, 5: 73, 6: 73}  # SURVEY.md 8d (A, breakup)
+
+
+class Spy:
+    """counts the (sub-)steps a run executes and the super-droplets each one works on (the
+    working length), and times the fused launches with CUDA events: wraps the two C-ABI entry
+    points every (sub-)step goes through -- pysdm_b200.methods.fused_collision_step (fused path)
+    or compute_gamma (method-level path)"""
+
+    def __init__(self):
+        self.sd_substeps = self.substeps = 0
+        self.events = []
+
+    def __enter__(self):
+        import torch
+        from pysdm_b200 import methods as m
+
+        self.m, self.real_fused, self.real_gamma = m, m.fused_collision_step, m.compute_gamma
+
+        def fused(**kw):
+            self.substeps += 1
+            self.sd_substeps += int(kw["length"])
+            beg, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            beg.record()
+            err = self.real_fused(**kw)
+            end.record()
+            self.events.append((beg, end))
+            return err
+
+        def gamma(prob, rand, idx, length, *args):
+            self.substeps += 1
+            self.sd_substeps += int(length)
+            return self.real_gamma(prob, rand, idx, length, *args)
+
+        m.fused_collision_step, m.compute_gamma = fused, gamma
+        return self
+
+    def __exit__(self, *exc):
+        self.m.fused_collision_step, self.m.compute_gamma = self.real_fused, self.real_gamma
+
+    def fused_ms(self):
+        return sum(a.elapsed_time(b) for a, b in self.events)
+
+
+def run(config, backend_name, steps, log2=None, peak_gbs=None):
     from PySDM import Builder, Formulae
     from PySDM.environments import Box
 
@@ -103,11 +149,15 @@ def run(config, backend_name, steps, log2=None):
                       "multiplicity": np.full(
                           n_sd, c.get("multiplicity", int(100e6 * c["dv"] / c["sd_per_cell"])),
                           dtype=np.int64)}
+        if c.get("n_attr", 1) == 3:  # environments/kinematic_2d.py:63-64,84
+            attributes["dry volume"] = volume * 1e-3
+            attributes["kappa times dry volume"] = volume * 0.6e-3
     else:
         attributes = {"volume": volume, "multiplicity": np.full(
             n_sd, max(1, int(c["norm"] / n_sd)), dtype=np.int64)}
     formulae = Formulae(seed=44, **c["fkw"])
-    if backend_name.startswith("B200"):  # "B200F": FusedCoalescence instead of Coalescence
+    gpu = backend_name.startswith("B200")
+    if gpu:  # "B200F": FusedCoalescence instead of Coalescence
         from pysdm_b200 import B200
 
         backend = B200(formulae)
@@ -117,28 +167,79 @@ def run(config, backend_name, steps, log2=None):
         backend = CPU(formulae)
     builder = Builder(n_sd=n_sd, backend=backend, environment=env)
     builder.add_dynamic(dynamics(config, fused=backend_name == "B200F"))
+    for name in ("dry volume", "kappa times dry volume"):
+        if name in attributes:
+            builder.request_attribute(name)
     particulator = builder.build(attributes=attributes, products=())
     particulator.run(2)  # warm-up (JIT / workspaces)
-    sync = (lambda: None)
-    if backend_name.startswith("B200"):
+    dyn = particulator.dynamics["Collision"]
+    out = {"config": c["name"], "backend": backend_name, "n_sd": n_sd, "steps": steps}
+    if gpu:
         import torch
 
-        sync = torch.cuda.synchronize
-    sync()
-    t0 = time.perf_counter()
-    particulator.run(steps)
-    sync()
-    dt = time.perf_counter() - t0
-    dyn = particulator.dynamics["Collision"]
-    if backend_name == "B200F" and KERNEL_ONLY:
+        beg, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        with Spy() as spy:
+            t0 = time.perf_counter()
+            beg.record()
+            particulator.run(steps)
+            end.record()
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+        ms = beg.elapsed_time(end) / steps  # CUDA events around the steps (host overhead included)
+        algorithmic = BYTES_PER_SD[config] * spy.sd_substeps / steps
+        out.update({
+            "ms_per_step": ms, "wall_ms_per_step": dt / steps * 1e3,
+            "sd_steps_per_s": n_sd / (ms * 1e-3),
+            "substeps_per_step": spy.substeps / steps,
+            "fused_steps": int(getattr(dyn, "n_fused_steps", 0)),
+            "roofline": {
+                "bound": "hbm", "unit": "GB/s", "algorithmic_bytes_per_step": algorithmic,
+                "bytes_per_sd_substep": BYTES_PER_SD[config],
+                "achieved": algorithmic / (ms * 1e-3) / 1e9, "peak": peak_gbs,
+                "frac": None if not peak_gbs else algorithmic / (ms * 1e-3) / 1e9 / peak_gbs,
+                "fused_kernel_ms_per_step": spy.fused_ms() / steps if spy.events else None,
+                "frac_fused_kernels_only": None if not (peak_gbs and spy.events) else
+                algorithmic / (spy.fused_ms() / steps * 1e-3) / 1e9 / peak_gbs}})
+    else:
+        t0 = time.perf_counter()
+        particulator.run(steps)
+        dt = time.perf_counter() - t0
+        out.update({"ms_per_step": dt / steps * 1e3, "sd_steps_per_s": n_sd * steps / dt,
+                    "threads": os.environ.get("NUMBA_NUM_THREADS", "default")})
+    if gpu and backend_name == "B200F" and KERNEL_ONLY:
         kernel_only(particulator, c, n_sd)
-    substeps = float(np.mean(dyn.stats_n_substep.to_ndarray())) if config else float(steps + 2)
-    print(json.dumps({
-        "config": c["name"], "backend": backend_name, "n_sd": n_sd, "steps": steps,
-        "ms_per_step": dt / steps * 1e3, "sd_steps_per_s": n_sd * steps / dt,
-        "substeps_since_start": substeps,
-        "threads": os.environ.get("NUMBA_NUM_THREADS", "default") if backend_name == "CPU" else None,
-        "super_droplets_left": int(particulator.attributes.super_droplet_count)}), flush=True)
+    out["super_droplets_left"] = int(particulator.attributes.super_droplet_count)
+    return out
+
+
+def all_configs(steps, peak_gbs, numba=True, cpu_log2=20):
+    """BASELINE configs[0..3] through `Builder(backend=B200())` (the plug-in call) at their
+    stated sizes, with the fused dynamic where it applies; the reference's Numba backend next
+    to each on a bounded sample (2^cpu_log2 SDs at most; SD-steps/s is size-normalised)"""
+    rows = []
+    for config in (0, 1, 2, 3):
+        fused = config != 2  # breakup runs on the method-level kernels
+        row = run(config, "B200F" if fused else "B200", steps, peak_gbs=peak_gbs)
+        row["baseline_config"] = f"configs[{config}]"
+        if numba:
+            try:
+                cpu = run(config, "CPU", 1, log2=min(cpu_log2, SETUP[config]["log2"]))
+                row["numba"] = {k: cpu[k] for k in ("n_sd", "ms_per_step", "sd_steps_per_s",
+                                                    "threads")}
+                row["speedup_vs_numba"] = row["sd_steps_per_s"] / cpu["sd_steps_per_s"]
+            except Exception as exc:  # pylint: disable=broad-except
+                row["numba"] = {"unavailable": f"{type(exc).__name__}: {exc}"[:200]}
+        rows.append(row)
+    return rows
+
+
+def pysdm_path(steps, peak_gbs):
+    """BASELINE configs[4] (the bench.py workload) through the unmodified PySDM orchestration on
+    the B200 backend: with the stock `Coalescence` (method-level kernels) and with the fused
+    dynamic"""
+    return {"stock_coalescence": run(4, "B200", steps, peak_gbs=peak_gbs),
+            "fused_coalescence": run(4, "B200F", steps, peak_gbs=peak_gbs)}
 
 
 KERNEL_ONLY = False
@@ -201,6 +302,10 @@ if __name__ == "__main__":
                     help="B200F: also time the fused launch alone with CUDA events")
     a = ap.parse_args()
     KERNEL_ONLY = a.kernel_only
+    _peak = None
+    if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")):
+        _peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     for cfg in (int(x) for x in a.configs.split(",")):
         for be in a.backends.split(","):
-            run(cfg, be, a.steps if be.startswith("B200") else a.cpu_steps, a.log2)
+            print(json.dumps(run(cfg, be, a.steps if be.startswith("B200") else a.cpu_steps,
+                                 a.log2, _peak)), flush=True)

@@ -56,6 +56,7 @@ SIGNATURES = {
     "pysdm_b200_fused_collision_step": (INT, (P, P)),
     "pysdm_b200_shuffle_local_batched": (INT, (P, P, P, I64, I64, I64, P, P)),
     "pysdm_b200_invert_index": (INT, (P, P, I64, P)),
+    "pysdm_b200_dependent_attributes": (INT, (P, I64, F64, F64, F64, F64, F64, P, P, P, P, P, P, P)),
     "pysdm_b200_interpolation": (INT, (P, P, I64, F64, P, P, P)),
     "pysdm_b200_terminal_velocity_rogers_yau": (INT, (P, P, I64, F64, F64, F64, F64, F64, P)),
     "pysdm_b200_power_series": (INT, (P, P, I64, I64, P, P, P)),
@@ -107,7 +108,10 @@ class FusedArgs(ctypes.Structure):
            ("berry_int_mask", I64), ("berry_unit", F64),
            ("adaptive", I64), ("dt_left", P), ("stats_n_substep", P), ("stats_dt_min", P),
            ("dt_min", F64), ("dt_max", F64), ("rank_to_cell", P), ("rank_info", P),
-           ("adaptive_end", P), ("length_dev", P)])
+           ("adaptive_end", P), ("length_dev", P),
+           ("dep_volume", P), ("dep_radius", P), ("dep_velocity", P), ("dep_table_b", P),
+           ("dep_table_c", P), ("dep_radius_scale", F64), ("dep_radius_exponent", F64),
+           ("dep_table_factor", F64), ("dep_radius_max", F64), ("dep_status", P)])
 
 
 KERNELS = {"Golovin": 0, "ConstantK": 1, "Linear": 2, "Geometric": 3, "Hydrodynamic": 4}

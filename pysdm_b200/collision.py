@@ -63,6 +63,43 @@ class Linear:
         m.elementwise("add", output, output, None, self.a)
 
 
+class Geometric:
+    """collision_kernels/geometric.py:15-22 with the Gunn-Kinzer fall velocity (PySDM's default
+    `terminal_velocity`): `sum_pair(radius)`, `**= 2`, `*= PI * collection_efficiency`,
+    `distance_pair(relative fall velocity)`, `*=`.  Radius and fall velocity are per-SD arrays
+    derived from the water mass (attributes/physics/{volume,radius,terminal_velocity}.py); the
+    simulation object owns them (`DeviceCollision.radius`, `.fall_velocity`) -- computed in one
+    pass up front, then kept current by the fused step for the super-droplets a coalescence
+    changed, or recomputed in full before every step of the method-level path."""
+    fused = "Geometric"
+    needs_dependents = True
+    PI = 3.141592653589793
+    PI_4_3 = PI * 4 / 3  # PySDM/physics/constants_defaults.py
+
+    def __init__(self, collection_efficiency=1.0):
+        self.a, self.b = self.PI * collection_efficiency, 0.0
+
+    def __call__(self, sim, output, flag):
+        m.pair_op("sum", output, sim.radius, flag, sim.idx, sim.length)
+        m.elementwise("pow", output, output, None, 2.0)
+        m.elementwise("mul", output, output, None, self.a)
+        m.pair_op("distance", sim.pair_tmp, sim.fall_velocity, flag, sim.idx, sim.length)
+        m.elementwise("mul", output, output, sim.pair_tmp)
+
+
+def gunn_kinzer_table(device):
+    """the reference's interpolation table (pysdm_b200/data, written by oracle/gen_gk_table.py
+    from the reference object) on the device"""
+    import os  # pylint: disable=import-outside-toplevel
+
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "gunn_kinzer_1949.npz")
+    with np.load(path) as table:
+        return {"table_b": torch.from_numpy(table["a"]).to(device),
+                "table_c": torch.from_numpy(table["b"]).to(device),
+                "table_factor": float(table["factor"]),
+                "radius_max": float(table["maximum_radius"])}
+
+
 class DeviceCollision:  # pylint: disable=too-many-instance-attributes
     """`Coalescence(collision_kernel=kernel, ...)` on a Box or a mesh of `n_cell` cells"""
 
@@ -138,17 +175,30 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.rnd = rnd
         self.substep = 0
         self._volume = full(self.n_sd, nan, f64)
+        self.n_launches = 0  # CUDA launches issued through the C-ABI (entry-point calls)
+        # gravitational kernels: radius and fall velocity per SD (see `Geometric`)
+        self.dependents = None
+        if getattr(kernel, "needs_dependents", False):
+            self.radius, self.fall_velocity = full(self.n_sd, nan, f64), full(self.n_sd, nan, f64)
+            self.pair_tmp = full(n_pairs, nan, f64)
+            self.dependents = {"volume": self._volume, "radius": self.radius,
+                               "velocity": self.fall_velocity,
+                               "radius_scale": 1 / kernel.PI_4_3, "radius_exponent": 1 / 3,
+                               "status": full(1, 0, i64), **gunn_kinzer_table(dev)}
+            self.refresh_dependents()
         self.dt_min_warning = False
         self.fused = fused
         self.n_fused_steps = 0
-        self.n_launches = 0  # CUDA launches issued through the C-ABI (entry-point calls)
+        self._epoch = 0
         self._healthy_host = torch.ones(1, dtype=i64).pin_memory()
         self._words_host = torch.zeros(4, dtype=i64).pin_memory()
-        # speculative stepping (step_async): gate word of the fused kernel, two pinned slots
-        # for the `healthy` flags in flight, the step whose flag has not been read yet
+        # speculative stepping (step_async): gate word of the fused kernel, a ring of pinned
+        # slots for the `healthy` flags in flight, the steps whose flags have not been read yet
         self.gate = full(1, 0, i64)
-        self._healthy_slots = torch.ones(2, dtype=i64).pin_memory()
-        self._pending = None
+        self.speculation_depth = 8
+        self._healthy_slots = torch.ones(self.speculation_depth + 1, dtype=i64).pin_memory()
+        self._in_flight = []  # (event, slot), oldest first
+        self._slot = 0
         # Builder.build: zero multiplicities are removed up front
         if bool((self.multiplicity == 0).any().item()):
             self.healthy.zero_()
@@ -158,6 +208,17 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
     def volume(self):
         m.volume_of_water_mass(self._volume, self.attributes[0], self.rho_w)
         return self._volume
+
+    def refresh_dependents(self):
+        """volume, radius and fall velocity of every super-droplet from the water mass (what the
+        orchestration recomputes when the water mass was marked updated), one pass"""
+        d = self.dependents
+        m.dependent_attributes(self.attributes[0], self.rho_w, volume=d["volume"],
+                               radius=d["radius"], velocity=d["velocity"], status=d["status"],
+                               **{k: d[k] for k in ("radius_scale", "radius_exponent",
+                                                    "table_factor", "radius_max", "table_b",
+                                                    "table_c")})
+        self.n_launches += 1
 
     def sort_by_cell_id(self):
         m.counting_sort_by_cell_id(self.tmp_idx, self.idx, self.cell_id, self.cell_idx,
@@ -178,6 +239,8 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.length = self.valid_n_sd = self.n_sd
         self.sorted = False
         self.n_launches += 1
+        if self.dependents is not None:
+            self.refresh_dependents()
         if bool((self.multiplicity == 0).any().item()):  # as Builder.build does up front
             self.healthy.zero_()
             self.sanitize()
@@ -293,15 +356,16 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
     # ---- speculative stepping: no host wait between fused launches ---------------------------
     def step_async(self, mark=None):
         """`step()` without the GPU idling while the host reads `healthy` (the reference reads
-        it after every step, impl/particle_attributes.py:67-73): the fused launch of this step
-        is queued first, then the flag of the PREVIOUS step is read.  If that step left zero
-        multiplicities, the launch just queued found its gate closed and did nothing
-        (pysdm_b200.h `gate`): its host bookkeeping is undone, the dead super-droplets are
-        removed and the step is issued again -- same results as step(), step by step.
-        Needs the device Philox generator (its stream position can be rewound); otherwise,
-        and whenever the fused step does not apply, this is step().  Call drain() before
-        reading state.  `mark`: a CUDA event recorded right behind the fused launch (timing)."""
-        if not isinstance(self.rnd, Random) or not self._fused_ok():
+        it after every step, impl/particle_attributes.py:67-73): fused launches are queued up to
+        `speculation_depth` steps ahead of the oldest flag that has not been read.  A launch
+        that leaves zero multiplicities closes the gate (pysdm_b200.h `gate`), so the launches
+        queued behind it find it closed and do nothing: their host bookkeeping is undone, the
+        dead super-droplets are removed and the steps are issued again -- same results as
+        step(), step by step.  Needs the device Philox generator (its stream position can be
+        rewound); otherwise, and whenever the fused step does not apply, this is step().
+        Call drain() before reading state.  `mark`: a CUDA event recorded right behind the
+        fused launch (timing)."""
+        if not isinstance(self.rnd, Random) or self.optimized_random or not self._fused_ok():
             self.drain()
             self.step()
             if mark is not None:
@@ -310,19 +374,31 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.step_fused(gated=True)
         if mark is not None:
             mark.record()
-        slot = 0 if self._pending is None else 1 - self._pending[1]
+        slot = self._slot
+        self._slot = (slot + 1) % self._healthy_slots.numel()
         self._healthy_slots[slot:slot + 1].copy_(self.healthy, non_blocking=True)
         event = torch.cuda.Event()
         event.record()
-        previous, self._pending = self._pending, (event, slot)
-        if previous is not None and not self._resolved_healthy(previous):
-            # undo the bookkeeping of the launch that did nothing, then redo the step
+        self._in_flight.append((event, slot))
+        # read the flags that have arrived; wait only when the ring is full
+        while self._in_flight and (len(self._in_flight) > self.speculation_depth
+                                   or self._in_flight[0][0].query()):
+            if not self._resolved_healthy(self._in_flight.pop(0)):
+                redo = len(self._in_flight)  # the launches queued behind it did nothing
+                self._undo(redo)
+                for _ in range(redo):
+                    self.step_async()
+                return
+
+    def _undo(self, n_steps):
+        """the last `n_steps` launches found the gate closed: undo their host bookkeeping, then
+        remove the dead super-droplets (what step() would have done after the unhealthy step)"""
+        if n_steps % 2:
             self.idx, self.tmp_idx = self.tmp_idx, self.idx
-            self.rnd.call -= 2
-            self.n_fused_steps -= 1
-            self._pending = None
-            self._remove_zero_multiplicities()
-            self.step_async(mark)
+        self.rnd.call -= 2 * n_steps
+        self.n_fused_steps -= n_steps
+        self._in_flight = []
+        self._remove_zero_multiplicities()
 
     def _resolved_healthy(self, pending):
         event, slot = pending
@@ -330,10 +406,13 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         return bool(self._healthy_slots[slot])
 
     def drain(self):
-        """waits for the step in flight and sanitizes after it, as step() would have"""
-        pending, self._pending = self._pending, None
-        if pending is not None and not self._resolved_healthy(pending):
-            self._remove_zero_multiplicities()
+        """waits for the steps in flight and sanitizes after them, as step() would have"""
+        while self._in_flight:
+            if not self._resolved_healthy(self._in_flight.pop(0)):
+                redo = len(self._in_flight)
+                self._undo(redo)
+                for _ in range(redo):
+                    self.step_async()
 
     def step_fused(self, gated=False):
         """one launch: csrc/fused.cu"""
@@ -344,6 +423,9 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
                 "stats_dt_min": self.stats_dt_min, "dt_min": self.dt_coal_range[0],
                 "dt_max": self.dt_coal_range[1], "rank_to_cell": self.rank_to_cell,
                 "rank_info": self.rank_info, "adaptive_end": self.adaptive_end}
+        if self.dependents is not None:
+            kw.update(radius=self.radius, fall_velocity=self.fall_velocity,
+                      dependents=self.dependents)
         if isinstance(self.rnd, Random) and not self.optimized_random:
             # uniforms generated in-kernel from the same stream
             kw.update(seed=self.rnd.seed, call_u01=self.rnd.call, call_rand=self.rnd.call + 1)
@@ -362,7 +444,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             kernel_a=self.kernel.a, kernel_b=self.kernel.b, timestep=self.dt, dv=self.dv,
             rho_w=self.rho_w, substeps=1 if self.adaptive else self.substeps,
             nf_slot=self.nf_slot, refresh_nf=not self.nf_valid, gate=self.gate if gated else None,
-            epoch=self.n_fused_steps + 1, **kw)
+            epoch=self._epoch + 1, **kw)
         m.check(err, "fused_collision_step")
         self.n_launches += 1 if self.nf_valid and not self.adaptive else 3
         self.nf_valid = not self.adaptive  # (cell_idx is re-sorted before every adaptive sub-step)
@@ -371,9 +453,12 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             self.tmp_idx[self.sorted_length:] = self.idx[self.sorted_length:]
         self.idx, self.tmp_idx = self.tmp_idx, self.idx
         self.n_fused_steps += 1
+        self._epoch += 1  # never reused: a closed gate carries the epoch of the launch that closed it
 
     def step_methods(self):
         """the reference's sequence of backend calls, one kernel (group) each"""
+        if self.dependents is not None:  # the orchestration's recalculation of derived attributes
+            self.refresh_dependents()
         pairs_rand, rand = self.get_random_arrays()
         self.permutation(pairs_rand, self.croupier == "local")
         cell_start = self.get_cell_start()

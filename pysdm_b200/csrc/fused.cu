@@ -53,6 +53,43 @@ PYSDM_EXPORT int pysdm_b200_invert_index(i64 *out, const i64 *in, i64 n, void *s
     return LAUNCH_CHECK();
 }
 
+__global__ void k_dependent_attributes(const double *__restrict__ mass, i64 n, DependentParams p,
+                                       double *__restrict__ volume, double *__restrict__ radius,
+                                       double *__restrict__ velocity, i64 *__restrict__ status)
+{
+    i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double vol, rad, vel;
+    const bool ok = dependents_of(mass[i], p, vol, rad, vel);
+    if (volume != nullptr) volume[i] = vol;
+    if (radius != nullptr) radius[i] = rad;
+    if (!ok && status != nullptr) status[0] = 1;
+    if (ok && velocity != nullptr) velocity[i] = vel;
+}
+
+PYSDM_EXPORT int pysdm_b200_dependent_attributes(const double *mass, i64 n, double rho_w,
+                                                 double radius_scale, double radius_exponent,
+                                                 double table_factor, double radius_max,
+                                                 const double *table_b, const double *table_c,
+                                                 double *volume, double *radius, double *velocity,
+                                                 i64 *status, void *stream)
+{
+    if (n <= 0) return 0;
+    if (velocity != nullptr && (table_b == nullptr || table_c == nullptr))
+        return (int)cudaErrorInvalidValue;
+    DependentParams p;
+    p.rho_w = rho_w;
+    p.radius_scale = radius_scale;
+    p.radius_exponent = radius_exponent;
+    p.table_factor = table_factor;
+    p.radius_max = radius_max;
+    p.table_b = table_b;
+    p.table_c = table_c;
+    k_dependent_attributes<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(
+        mass, n, p, volume, radius, velocity, status);
+    return LAUNCH_CHECK();
+}
+
 PYSDM_EXPORT int64_t pysdm_b200_fused_max_cell_size(void) { return kCtaPos; }
 
 // precondition of div_by(): b normal, moderate, significand not all ones
@@ -123,9 +160,15 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
         return dispatch_fused<KERNEL_LINEAR>(a, n_batches, philox, warp, aggregate, adaptive, st);
     case KERNEL_GEOMETRIC:
         if (a.radius == nullptr || a.fall_velocity == nullptr) return (int)cudaErrorInvalidValue;
+        if (a.dep_radius != nullptr && a.dep_velocity != nullptr &&
+            (a.dep_table_b == nullptr || a.dep_table_c == nullptr))
+            return (int)cudaErrorInvalidValue;
         return dispatch_fused<KERNEL_GEOMETRIC>(a, n_batches, philox, warp, aggregate, adaptive, st);
     case KERNEL_HYDRODYNAMIC:
         if (a.radius == nullptr || a.fall_velocity == nullptr) return (int)cudaErrorInvalidValue;
+        if (a.dep_radius != nullptr && a.dep_velocity != nullptr &&
+            (a.dep_table_b == nullptr || a.dep_table_c == nullptr))
+            return (int)cudaErrorInvalidValue;
         return dispatch_fused<KERNEL_HYDRODYNAMIC>(a, n_batches, philox, warp, aggregate, adaptive, st);
     default: return (int)cudaErrorInvalidValue;
     }

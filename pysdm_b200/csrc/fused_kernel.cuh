@@ -41,6 +41,7 @@
 // each is exact (bit-identical to the plain expression), with a guarded slow path.
 #pragma once
 #include "berry.cuh"
+#include "dependents.cuh"
 #include "philox.cuh"
 #include "pysdm_b200.h"
 #include "sdm_device.cuh"
@@ -250,11 +251,35 @@ __device__ __forceinline__ void process_hits(const FusedArgs &a, u32 pf, double 
                 a.multiplicity[sj] = nj_new;
                 a.multiplicity[sk] = nk_new;
             }
+            double new_mass = 0.0;
             for (i64 r_ = 0; r_ < a.n_attr; ++r_) {
                 double *row = a.attributes + r_ * a.n_sd;
                 const double v = fma(gamma, row[sj], row[sk]);
                 row[sk] = v;
                 if (!keep) row[sj] = v;
+                if (r_ == a.mass_row) new_mass = v;
+            }
+            if ((K == KERNEL_GEOMETRIC || K == KERNEL_HYDRODYNAMIC) && a.dep_radius != nullptr) {
+                // the attributes derived from the water mass, for the changed super-droplets only
+                DependentParams dp;
+                dp.rho_w = a.rho_w;
+                dp.radius_scale = a.dep_radius_scale;
+                dp.radius_exponent = a.dep_radius_exponent;
+                dp.table_factor = a.dep_table_factor;
+                dp.radius_max = a.dep_radius_max;
+                dp.table_b = a.dep_table_b;
+                dp.table_c = a.dep_table_c;
+                double vol, rad, vel;
+                const bool ok = dependents_of(new_mass, dp, vol, rad, vel);
+                if (!ok && a.dep_status != nullptr) a.dep_status[0] = 1;
+                if (a.dep_volume != nullptr) a.dep_volume[sk] = vol;
+                a.dep_radius[sk] = rad;
+                if (ok && a.dep_velocity != nullptr) a.dep_velocity[sk] = vel;
+                if (!keep) {
+                    if (a.dep_volume != nullptr) a.dep_volume[sj] = vol;
+                    a.dep_radius[sj] = rad;
+                    if (ok && a.dep_velocity != nullptr) a.dep_velocity[sj] = vel;
+                }
             }
             if (nj_new == 0 || nk_new == 0) {
                 a.healthy[0] = 0;

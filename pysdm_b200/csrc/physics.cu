@@ -20,6 +20,7 @@
 
 #include "common.cuh"
 #include "berry.cuh"
+#include "dependents.cuh"
 
 namespace {
 
@@ -71,26 +72,7 @@ __global__ void k_interpolation(double *__restrict__ output, const double *__res
                                 const double *__restrict__ c)
 {
     TID_OR_RETURN(n);
-    double r = radius[i];
-    if (r < 0) {
-        output[i] = 0;
-        return;
-    }
-    double fr = factor * r;
-    i64 r_id;
-    double frac;  // (factor * r) % 1
-    if (fr >= 0.0 && fr < 2251799813685248.0) {  // NaN takes the other branch
-        // exact, without the 64-bit conversion and the fmod loop: 2^52 + floor(fr) by a
-        // round-down add, the integer from its mantissa, fr - floor(fr) = fmod(fr, 1) exactly
-        const double t = __dadd_rd(fr, 4503599627370496.0);
-        r_id = (i64)((u64)__double_as_longlong(t) & 0x000FFFFFFFFFFFFFull);
-        frac = fr - (t - 4503599627370496.0);
-    } else {
-        r_id = (i64)fr;
-        frac = fmod(fr, 1.0);
-    }
-    double r_rest = frac / factor;
-    output[i] = b[r_id] + r_rest * c[r_id];
+    output[i] = table_interpolation(radius[i], factor, b, c);
 }
 
 __global__ void k_rogers_yau(double *__restrict__ values, const double *__restrict__ radius, i64 n,

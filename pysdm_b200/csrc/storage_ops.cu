@@ -7,6 +7,7 @@
 #include <math.h>
 
 #include "primitives.cuh"
+#include "dependents.cuh"
 
 // ---- elementwise ---------------------------------------------------------------
 enum EwOp {
@@ -22,20 +23,6 @@ enum EwOp {
     EW_ABS = 9,
     EW_MOD = 10  // Python float modulo (result takes the sign of the divisor)
 };
-
-__device__ __forceinline__ double signed_pow(double x, double e)
-{
-    double s = x > 0 ? 1.0 : (x < 0 ? -1.0 : (x == 0 ? 0.0 : x));
-    double ax = fabs(x);
-    double p;
-    if (e == 2.0)
-        p = ax * ax;  // exact-rounded, what libm's pow returns for squares
-    else if (e == 1.0)
-        p = ax;
-    else
-        p = pow(ax, e);
-    return s * p;
-}
 
 __device__ __forceinline__ double py_mod(double a, double b)
 {

@@ -60,6 +60,7 @@ def make_fused_coalescence():
             super().__init__(*args, **kwargs)
             self.n_fused_steps = 0
             self._nf_slot = self._status = self._nf_facts = self._rank_info = None
+            self._dependents = None  # derived attributes the fused step keeps current itself
 
         def register(self, builder):
             super().register(builder)
@@ -69,10 +70,41 @@ def make_fused_coalescence():
             self._status = torch.zeros(1, dtype=torch.int64, device=dev)
             self._rank_info = torch.zeros(self.particulator.mesh.n_cell, dtype=torch.int64,
                                           device=dev)
+            self._dependents = self._dependent_chain(builder)
+
+        def _dependent_chain(self, builder):
+            """the attributes PySDM derives from the water mass for the gravitational kernels --
+            "volume" (attributes/physics/volume.py), "radius" (radius.py:15-17), the fall
+            velocity (terminal_velocity.py with the Gunn-Kinzer `interpolation`,
+            dynamics/terminal_velocity/gunn_and_kinzer.py:128-133) -- when they are exactly these
+            stock classes: the fused step then refreshes them for the super-droplets a
+            coalescence changed (pysdm_b200.h `dep_*`), instead of the orchestration
+            recomputing all of them after every (sub-)step in five launches and a host sync.
+            None = leave it to the orchestration."""
+            name = type(self.collision_kernel).__name__
+            if name != "Geometric" and not isinstance(self.collision_kernel, Parameterized):
+                return None
+            formulae = builder.particulator.backend.formulae
+            if getattr(formulae.particle_shape_and_density, "__name__", "") != "LiquidSpheres":
+                return None
+            mass, volume, radius, velocity = (builder.get_attribute(k) for k in (
+                "water mass", "volume", "radius", "relative fall velocity"))
+            approximation = getattr(velocity, "approximation", None)
+            if ([type(x).__name__ for x in (mass, volume, radius, velocity, approximation)]
+                    != ["ViewWaterMass", "Volume", "Radius", "TerminalVelocity", "GunnKinzer1949"]):
+                return None
+            return {"chain": (mass, volume, radius, velocity), "approximation": approximation,
+                    "radius_scale": 1 / formulae.constants.PI_4_3, "radius_exponent": 1 / 3,
+                    "status": torch.zeros(1, dtype=torch.int64, device=self.gamma.data.device)}
 
         def __call__(self):
             fused_before = self.n_fused_steps
             super().__call__()
+            if self._dependents is not None and self.n_fused_steps > fused_before:
+                if int(self._dependents["status"].item()):  # gunn_and_kinzer.py:129-133
+                    raise ValueError(
+                        f"Radii can be interpolated up to "
+                        f"{self._dependents['approximation'].maximum_radius} m")
             if self.adaptive and self.n_fused_steps > fused_before:
                 # the reference looks at this after every sub-step (collision.py:276-277); the
                 # fused sub-steps leave it to one look per time step (stats_dt_min only falls)
@@ -134,6 +166,15 @@ def make_fused_coalescence():
                 # terminal_velocity.py) -- the operands geometric.py:15-22 gathers
                 kw["radius"] = attrs["radius"].data
                 kw["fall_velocity"] = attrs["relative fall velocity"].data
+                if self._dependents is not None:
+                    dep, approx = self._dependents, self._dependents["approximation"]
+                    kw["dependents"] = {
+                        "volume": attrs["volume"].data, "radius": kw["radius"],
+                        "velocity": kw["fall_velocity"], "table_b": approx.a.data,
+                        "table_c": approx.b.data, "table_factor": approx.factor,
+                        "radius_max": approx.maximum_radius, "status": dep["status"],
+                        "radius_scale": dep["radius_scale"],
+                        "radius_exponent": dep["radius_exponent"]}
             substeps = 1
             if self.adaptive:
                 kw["adaptive"] = {
@@ -170,5 +211,13 @@ def make_fused_coalescence():
             attrs.mark_updated("multiplicity")
             for key in attrs.get_extensive_attribute_keys():
                 attrs.mark_updated(key)
+            if "dependents" in kw:
+                # volume / radius / fall velocity are current already: stamp them as derived from
+                # the water mass as it is now (DerivedAttribute.update, attributes/impl/
+                # derived_attribute.py:18-26, compares these time stamps), in dependency order
+                for attribute in self._dependents["chain"]:
+                    for dependency in attribute.dependencies:
+                        dependency.update()
+                    attribute.timestamp = sum(d.timestamp for d in attribute.dependencies)
 
     return FusedCoalescence

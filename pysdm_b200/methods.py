@@ -265,7 +265,8 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
                          max_cell, kernel, kernel_a=0.0, kernel_b=0.0, timestep, dv, rho_w,
                          substeps=1, mass_row=0, u01=None, rand=None, seed=0, call_u01=0,
                          call_rand=0, nf_slot, refresh_nf=True, gate=None, epoch=1, radius=None,
-                         fall_velocity=None, berry_params=None, berry_unit=1.0, adaptive=None):
+                         fall_velocity=None, berry_params=None, berry_unit=1.0, adaptive=None,
+                         dependents=None):
     """one Collision.step() in one launch; returns the CUDA error code (9 = a cell is
     larger than the fused path supports -> use the method-level functions).  kernel
     "Geometric": kernel_a = PI * collection_efficiency, `radius` and `fall_velocity` = the
@@ -300,12 +301,33 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         args.rank_info = _pi(adaptive["rank_info"])
         args.adaptive_end = _pi(adaptive.get("adaptive_end"))
         args.length_dev = _pi(adaptive.get("length_dev"))
+    if dependents is not None:  # see pysdm_b200_fused_args `dep_*`
+        args.dep_volume = _pf(dependents.get("volume"))
+        args.dep_radius = _pf(dependents["radius"])
+        args.dep_velocity = _pf(dependents.get("velocity"))
+        args.dep_table_b = _pf(dependents.get("table_b"))
+        args.dep_table_c = _pf(dependents.get("table_c"))
+        args.dep_radius_scale = float(dependents["radius_scale"])
+        args.dep_radius_exponent = float(dependents["radius_exponent"])
+        args.dep_table_factor = float(dependents.get("table_factor", 0.0))
+        args.dep_radius_max = float(dependents.get("radius_max", float("inf")))
+        args.dep_status = _pi(dependents.get("status"))
     if berry_params is not None:
         assert len(berry_params) == 13
         args.berry_params = (ctypes.c_double * 13)(*[float(v) for v in berry_params])
         args.berry_int_mask = int_mask_of(berry_params)
         args.berry_unit = float(berry_unit)
     return _lib.load().pysdm_b200_fused_collision_step(ctypes.byref(args), _stream())
+
+
+def dependent_attributes(mass, rho_w, *, radius_scale, radius_exponent, table_factor=0.0,
+                         radius_max=float("inf"), table_b=None, table_c=None, volume=None,
+                         radius=None, velocity=None, status=None):
+    """volume / radius / Gunn-Kinzer fall velocity of every super-droplet in one pass"""
+    check(_lib.load().pysdm_b200_dependent_attributes(
+        _pf(mass), mass.numel(), float(rho_w), float(radius_scale), float(radius_exponent),
+        float(table_factor), float(radius_max), _pf(table_b), _pf(table_c), _pf(volume),
+        _pf(radius), _pf(velocity), _pi(status), _stream()), "dependent_attributes")
 
 
 # ---- terminal velocities, collection efficiency (csrc/physics.cu) ---------------------------

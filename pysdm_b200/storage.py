@@ -295,6 +295,9 @@ class Storage(StorageBase):
             self.data = self.data.clone()
 
     def download(self, target, reshape=False):
+        if isinstance(target, torch.Tensor):  # straight into (pinned) host memory
+            target.copy_(self.data.reshape(target.shape))
+            return
         host = self.data.cpu().numpy()
         if reshape:
             host = host.reshape(target.shape)
@@ -304,6 +307,9 @@ class Storage(StorageBase):
         return self.data.cpu().numpy().copy()
 
     def upload(self, data):
+        if isinstance(data, torch.Tensor):  # (pinned) host tensor of the storage's own dtype
+            self.data.copy_(data.reshape(self.data.shape), non_blocking=True)
+            return
         host = np.ascontiguousarray(np.asarray(data).astype(self.dtype, casting="safe"))
         self.data.copy_(torch.from_numpy(host).reshape(self.data.shape))
 

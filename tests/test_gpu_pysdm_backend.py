@@ -481,7 +481,16 @@ def test_fused_coalescence_geometric(pysdm, kernel, grid, host_rng):
             assert_same_f64(a["attributes"], b["attributes"], f"step {step}: attributes")
         for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate"):
             np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
+        # the derived attributes: the fused step refreshes them for the super-droplets a
+        # coalescence changed and stamps them as current; the stock path recomputes all of them
+        for name in ("volume", "radius", "relative fall velocity"):
+            x, y = sut.attributes[name].to_ndarray(), ref.attributes[name].to_ndarray()
+            if host_rng:
+                np.testing.assert_allclose(x, y, rtol=1e-12, atol=0, err_msg=name)
+            else:
+                assert_same_f64(x, y, f"step {step}: {name}")
     assert sut.dynamics["Collision"].n_fused_steps == 6
+    assert sut.dynamics["Collision"]._dependents is not None  # pylint: disable=protected-access
     assert int(snapshot(ref)["coalescence_rate"].sum()) > 0
 
 

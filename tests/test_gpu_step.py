@@ -4,6 +4,8 @@ produced (tests/golden/scenario_*.npz) and (b) the CPU oracle on larger seeded i
 Bit-exact: permutation, pair flags, gamma (sign of zero included), multiplicities,
 counters and -- for coalescence -- the attributes too."""
 
+import os
+
 import numpy as np
 import pytest
 
@@ -338,3 +340,67 @@ class _Host:  # pylint: disable=too-few-public-methods
 
     def __getattr__(self, name):
         return self.sim.host(name)
+
+
+@pytest.mark.parametrize("mode", ("fixed", "adaptive_optrand"))
+@pytest.mark.parametrize("fused", (True, False))
+def test_geometric_standalone_against_oracle(fused, mode):
+    """BASELINE configs[3] in kind without PySDM in the process: `DeviceCollision` with the
+    Geometric kernel (radius and Gunn-Kinzer fall velocity derived from the water mass; the
+    fused step refreshes them only for the super-droplets a coalescence changed, the
+    method-level path recomputes them in full before every step), A = 3 attributes, cells of
+    ~128, adaptive time step with `optimized_random` -- against the oracle, which recomputes
+    the derived attributes in full like the orchestration.  Radii go through CUDA's pow here
+    and glibc's there: integers, permutation and gamma must still agree (flips are counted),
+    attributes to 1e-12."""
+    from oracle.sdm_step import Geometric as OGeometric  # pylint: disable=import-outside-toplevel
+
+    table = np.load(os.path.join(os.path.dirname(__file__), "..", "pysdm_b200", "data",
+                                 "gunn_kinzer_1949.npz"))
+    rng = np.random.default_rng(31)
+    n_cell = 96
+    sizes = rng.poisson(128, n_cell)
+    cell_id = np.repeat(np.arange(n_cell), sizes)
+    n_sd = len(cell_id)
+    radius = 10e-6 * np.exp(0.47 * rng.standard_normal(n_sd))
+    radius[rng.random(n_sd) < 0.02] *= 4.0
+    volume = 4 / 3 * np.pi * radius ** 3
+    dv = (1500 / 512) ** 2
+    pop = {"multiplicity": rng.integers(1, 2 * int(100e6 * dv / 128), n_sd).astype(np.int64),
+           "water_mass": 1000.0 * volume, "cell_id": cell_id, "n_cell": n_cell,
+           "extra_attributes": [volume * 1e-3, volume * 0.6e-3]}
+    common = dict(dt=5.0, dv=dv, seed=77)
+    if mode == "adaptive_optrand":
+        common.update(adaptive=True, optimized_random=True, dt_coal_range=(0.1, 5.0))
+    ora = OracleCollision(kernel=OGeometric(1.0, (table["a"], table["b"], float(table["factor"]),
+                                                  float(table["maximum_radius"]))),
+                          **pop, **common)
+    dev = device_sim(kernel=device_kernel("Geometric", collection_efficiency=1.0), host_rng=True,
+                     fused=fused, **pop, **common)
+    for step in range(4):
+        ora()
+        dev()
+        what = f"geometric {mode} step {step}"
+        n = ora.length
+        assert dev.length == n, what
+        np.testing.assert_array_equal(dev.host("idx")[:n], ora.idx[:n], what)
+        np.testing.assert_array_equal(dev.host("flag")[:n], ora.flag[:n], what)
+        flips = int((dev.host("gamma") != ora.gamma).sum())
+        assert flips == 0, f"{what}: {flips} gamma values differ (integer-boundary flips)"
+        np.testing.assert_array_equal(dev.host("multiplicity"), ora.multiplicity, what)
+        np.testing.assert_allclose(dev.host("attributes"), ora.attributes, rtol=1e-12, atol=0)
+        for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate",
+                  "stats_n_substep"):
+            np.testing.assert_array_equal(dev.host(k), getattr(ora, k), f"{what}: {k}")
+        # the derived attributes the fused step maintains == a full recomputation
+        np.testing.assert_allclose(dev.host("radius")[ora.idx[:n]], ora.kernel.radius[ora.idx[:n]],
+                                   rtol=1e-14, atol=0, err_msg=what)
+        kept = dev.host("radius").copy()
+        dev.refresh_dependents()
+        np.testing.assert_array_equal(dev.host("radius").view(np.int64), kept.view(np.int64),
+                                      f"{what}: radius kept current by the step != recomputed")
+    assert ora.coalescence_rate.sum() > 0
+    if mode != "fixed":
+        assert ora.stats_n_substep.max() > 4, "the time step was never cut"
+    if fused:
+        assert dev.n_fused_steps >= 4

@@ -224,7 +224,7 @@ def reference_arm(args):
 
 # ---- clocks: NVML through ctypes (no fork, no extra dependency) ------------------------------
 class ClockSampler(threading.Thread):
-    """samples SM clock and throttle reasons of one GPU every 2 ms while the timed region runs,
+    """samples SM clock and throttle reasons of one GPU every 0.5 ms while the timed region runs,
     straight from libnvidia-ml.so.1 (a query takes ~0.1 ms; nothing is forked)"""
 
     REASONS = (("sw_power_cap", 0x4), ("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20),
@@ -276,7 +276,7 @@ class ClockSampler(threading.Thread):
             return
         while not self.stop_flag.is_set():
             self.sample()
-            self.stop_flag.wait(0.002)
+            self.stop_flag.wait(0.0005)
 
     def summary(self):
         self.stop_flag.set()

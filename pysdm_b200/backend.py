@@ -64,6 +64,10 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
         # cell caretakers made by this backend, by the device pointer of the cell_start they
         # last sorted into (weak references: a caretaker lives as long as its ParticleAttributes)
         self._caretakers = {}
+        # device pointers of index tensors known to hold the identity permutation (written by
+        # identity_index, not sorted since): lets a caretaker tell a sort under the identity
+        # cell order, after which a repeated sort of the untouched idx is a no-op
+        self._identity_ptrs = set()
         BackendMethods.__init__(self)
 
     @property
@@ -71,9 +75,9 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
         return float(self.formulae.constants.rho_w)
 
     # ---- index methods (index_methods.py) ------------------------------------------------
-    @staticmethod
-    def identity_index(idx):  # :13-20
+    def identity_index(self, idx):  # :13-20
         m.identity_index(idx)
+        self._identity_ptrs.add(idx.data_ptr())
 
     @staticmethod
     def shuffle_global(idx, length, u01):  # :22-30
@@ -98,9 +102,9 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
         else:
             m.shuffle_local(idx, u01, cell_start, facts.length, facts.max_cell)
 
-    @staticmethod
-    def sort_by_key(idx, attr):  # :46-48
+    def sort_by_key(self, idx, attr):  # :46-48
         m.sort_by_key(idx.data, attr.data)
+        self._identity_ptrs.discard(idx.data.data_ptr())
 
     @staticmethod
     def remove_zero_n_or_flagged(multiplicity, idx, length):  # collisions_methods.py:664-680
@@ -112,7 +116,7 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
 
     def make_cell_caretaker(self, idx_shape, idx_dtype, cell_start_len, scheme="default"):
         """collisions_methods.py:587-631: owns tmp_idx, swaps the .data of idx and tmp_idx"""
-        registry = self._caretakers
+        registry, identity_ptrs = self._caretakers, self._identity_ptrs
 
         class CellCaretaker:  # pylint: disable=too-few-public-methods,too-many-instance-attributes
             def __init__(self):
@@ -120,6 +124,7 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
                 self.tmp_idx = Storage.empty(idx_shape, idx_dtype)
                 # facts of the last sort (for shuffle_local and the fused step)
                 self.length = self.max_cell = None
+                self.identity_sort = False  # the last sort ran under the identity cell order
                 self.cell_start_ref = lambda: None
                 self.n_sorts = 0
                 self.rank_to_cell = torch.arange(cell_start_len - 1, dtype=torch.int64,
@@ -132,6 +137,7 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
                 m.invert_index(self.rank_to_cell, cell_idx.data)
                 self.length = int(len(idx))
                 self.max_cell = m.max_cell_size(cell_start.data)
+                self.identity_sort = cell_idx.data.data_ptr() in identity_ptrs
                 self.cell_start_ref = weakref.ref(cell_start.data)
                 self.n_sorts += 1
                 for key in [k for k, v in registry.items() if v() is None]:

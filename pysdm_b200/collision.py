@@ -139,6 +139,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.cell_idx = torch.arange(self.n_cell, dtype=i64, device=dev)
         self.cell_start = full(self.n_cell + 1, 0, i64)
         self.sorted = False
+        self._cell_idx_identity, self._sort_identity = True, False
         self.sorted_length = 0
         self.max_cell = None
         # words the host reads back after a step: [0] healthy, [1:3] the fused adaptive
@@ -226,6 +227,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.idx, self.tmp_idx = self.tmp_idx, self.idx
         m.invert_index(self.rank_to_cell, self.cell_idx)  # the cell each rank of cell_start holds
         self.sorted = True
+        self._sort_identity = self._cell_idx_identity
         self.sorted_length = self.length  # = cell_start[-1], kept on the host
         self.max_cell = None
         self.nf_valid = False
@@ -301,6 +303,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             self.dt_left.fill_(self.dt)
             while self.length != 0:
                 m.sort_by_key(self.cell_idx, self.dt_left)
+                self._cell_idx_identity = False
                 if self._fused_ok():
                     # the launch also leaves adaptive_sdm_end's result next to `healthy`: one
                     # read-back per sub-step (valid unless SDs were removed: the reference then
@@ -320,7 +323,13 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
                 self.length = end
             self.length = self.valid_n_sd
             m.identity_index(self.cell_idx)
-            self.sort_by_cell_id()
+            self._cell_idx_identity = True
+            if self.sorted and self._sort_identity and self.sorted_length == self.length:
+                # idx is still in the order of a sort under the identity cell order: the stable
+                # re-sort of reset_cell_idx (impl/particle_attributes.py:86-88) would change nothing
+                self.nf_valid = False
+            else:
+                self.sort_by_cell_id()
         self.substep = 0
 
     def run(self, steps):

@@ -66,7 +66,7 @@ constexpr int kCtaPos = 8192, kCtaCells = 256;  // CTA group: positions / cells 
 constexpr int kWarpPos = PYSDM_WARP_POS, kWarpCells = 32;  // warp group
 static_assert(kWarpCells <= 32, "cell number and pair role share one byte (5 + 2 bits)");
 constexpr double kTwo52 = 4503599627370496.0;    // 2^52
-constexpr i64 kCidMask = ((i64)1 << 62) - 1;     // rank_info / cidv (adaptive): cell id | parity << 62
+constexpr i64 kCidMask = ((i64)1 << 61) - 1;     // rank_info / cidv (adaptive): cell id | idle << 61 | parity << 62
 
 // ---- exact arithmetic helpers without XU-pipe instructions ---------------------------------
 // (double)n for 0 <= n < 2^52 by mantissa insertion; other values take the conversion
@@ -403,8 +403,18 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     // the parity of cell_start[cell_idx[cell id]], the reference point find_pairs counts even
     // positions from (pair_methods.py:40; cell_idx is consumed as cell -> rank but was re-sorted
     // by dt_left since idx was sorted, quirk A2), both prepared per rank by k_fused_norm_factor
+    // A cell that has used up its time step (dt_left == 0) takes dt_todo = 0: its probabilities
+    // are scaled to zero whatever they are, and they would only matter for stats_dt_min -- which
+    // cannot change while it is NaN (its initial value; quirk A9).  Such "idle" cells (most cells
+    // from the second sub-step on) skip the kernel evaluation and its gathers altogether.
     if (kAdaptive)
-        for (int c = gt; c < ncb; c += G::kSize) cidv[c] = a.rank_info[c0 + c];
+        for (int c = gt; c < ncb; c += G::kSize) {
+            const i64 info = a.rank_info[c0 + c];
+            const i64 cid = info & kCidMask;
+            const double s = a.stats_dt_min[cid];
+            const bool idle = a.dt_left[cid] == 0.0 && s != s;
+            cidv[c] = info | ((i64)idle << 61);
+        }
     group_sync<kWarp>();
     // local positions below len_local are inside the working length
     const i64 len_rel = length - base_al;
@@ -840,7 +850,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
 
     // ---- pass A ----------------------------------------------------------------------------
     for (int it = 0; it < n_iter; ++it) {
-        bool has[2], dflt[2];
+        bool has[2], dflt[2], idle[2];
         int pf[2];
         u32 j[2], k[2];
         i64 nj[2], nk[2];
@@ -867,19 +877,22 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
             j[h] = k[h] = 0;
             nj[h] = nk[h] = 1;
             mj[h] = mk[h] = nf[h] = 0.0;
+            idle[h] = false;
             if (has[h]) {
                 j[h] = sd[phys(pf[h])];
                 k[h] = sd[phys(pf[h] + 1)];
+                idle[h] = ((cidv[cellof[pf[h]] & kCellMask] >> 61) & 1) != 0;
             } else {
                 dflt[h] = default_slot(lp0, v0, lp1 < P);
             }
-            if (has[h] || dflt[h]) nf[h] = nf_b[dl];
+            if ((has[h] && !idle[h]) || dflt[h]) nf[h] = nf_b[dl];
         }
 #pragma unroll
         for (int h = 0; h < 2; ++h)
             if (has[h]) {
                 nj[h] = a.multiplicity[j[h]];
                 nk[h] = a.multiplicity[k[h]];
+                if (idle[h]) continue;
                 if (K != KERNEL_CONSTANT_K) {
                     mj[h] = mass[j[h]];
                     mk[h] = mass[k[h]];
@@ -910,19 +923,23 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
                     out_b[(u32)pf[h]] = (i64)sj;
                     out_b[(u32)pf[h] + 1] = (i64)sk;
                 }
-                double kernel_temp;
-                if (K == KERNEL_GEOMETRIC) {
-                    kernel_temp = geometric_kernel_temp(m_j, m_k, uj[h], uk[h], a.kernel_a);
-                } else if (K == KERNEL_HYDRODYNAMIC) {
-                    kernel_temp = hydrodynamic_kernel_temp(a, m_j, m_k, uj[h], uk[h]);
-                } else {
-                    double vsum = 0.0;
-                    if (K != KERNEL_CONSTANT_K)
-                        vsum = div_by(m_j, a.rho_w, rho_rcp, rho_ok) + div_by(m_k, a.rho_w, rho_rcp, rho_ok);
-                    kernel_temp = kernel_temp_of<K>(vsum, a.kernel_a, a.kernel_b);
+                double prob = 0.0;  // idle cell: the scaled probability is 0 in any case
+                if (!idle[h]) {
+                    double kernel_temp;
+                    if (K == KERNEL_GEOMETRIC) {
+                        kernel_temp = geometric_kernel_temp(m_j, m_k, uj[h], uk[h], a.kernel_a);
+                    } else if (K == KERNEL_HYDRODYNAMIC) {
+                        kernel_temp = hydrodynamic_kernel_temp(a, m_j, m_k, uj[h], uk[h]);
+                    } else {
+                        double vsum = 0.0;
+                        if (K != KERNEL_CONSTANT_K)
+                            vsum = div_by(m_j, a.rho_w, rho_rcp, rho_ok) +
+                                   div_by(m_k, a.rho_w, rho_rcp, rho_ok);
+                        kernel_temp = kernel_temp_of<K>(vsum, a.kernel_a, a.kernel_b);
+                    }
+                    prob = i64_to_f64(n_j) * kernel_temp;
+                    prob = prob * nf[h];
                 }
-                double prob = i64_to_f64(n_j) * kernel_temp;
-                prob = prob * nf[h];
                 gamma_b[dl] = prob;
                 if (prob != 0.0) {  // pair_indices: prob == 0 skips the pair (:360-362)
                     const i64 prop = floordiv_sorted(n_j, n_k);

@@ -61,6 +61,7 @@ def make_fused_coalescence():
             self.n_fused_steps = 0
             self._nf_slot = self._status = self._nf_facts = self._rank_info = None
             self._dependents = None  # derived attributes the fused step keeps current itself
+            self._last_facts = None  # caretaker of the sort the last fused (sub-)step ran on
 
         def register(self, builder):
             super().register(builder)
@@ -70,6 +71,8 @@ def make_fused_coalescence():
             self._status = torch.zeros(1, dtype=torch.int64, device=dev)
             self._rank_info = torch.zeros(self.particulator.mesh.n_cell, dtype=torch.int64,
                                           device=dev)
+            self._words = torch.zeros(4, dtype=torch.int64, device=dev)  # [healthy, end, ...]
+            self._words_host = torch.zeros(4, dtype=torch.int64).pin_memory()
             self._dependents = self._dependent_chain(builder)
 
         def _dependent_chain(self, builder):
@@ -99,7 +102,10 @@ def make_fused_coalescence():
 
         def __call__(self):
             fused_before = self.n_fused_steps
-            super().__call__()
+            if self.enable and self.adaptive and self._kernel_name() is not None:
+                self._adaptive_loop()  # (falls back per sub-step when a cell is too large)
+            else:
+                super().__call__()
             if self._dependents is not None and self.n_fused_steps > fused_before:
                 if int(self._dependents["status"].item()):  # gunn_and_kinzer.py:129-133
                     raise ValueError(
@@ -111,8 +117,37 @@ def make_fused_coalescence():
                 if self.stats_dt_min.amin() == self.dt_coal_range[0]:
                     warnings.warn("adaptive time-step reached dt_min")
 
-        def _fused_plan(self):
-            """(kernel name, a, b, caretaker of the current sort) or None"""
+        def _adaptive_loop(self):
+            """`Collision.__call__` for the adaptive time step (collision.py:178-194), call for
+            call, with the fused sub-step: the launch also computes adaptive_sdm_end's result
+            (pysdm_b200.h `adaptive_end`), so one read-back per sub-step brings `healthy` and the
+            next working length instead of two synchronising calls"""
+            part, attrs = self.particulator, self.particulator.attributes
+            self.dt_left[:] = part.dt
+            in_order = False
+            while attrs.get_working_length() != 0:
+                attrs.cell_idx.sort_by_key(self.dt_left)
+                end = self.step(want_end=True)
+                in_order = end is not None
+                if end is None:  # not a fused sub-step, or super-droplets were removed
+                    end = part.adaptive_sdm_end(self.dt_left)
+                attrs.cut_working_length(end)
+            attrs.reset_working_length()
+            facts = self._last_facts
+            if (in_order and facts is not None and facts.identity_sort
+                    and facts.length == attrs.get_working_length()):
+                # idx is still in the order of a sort under the identity cell order (the local
+                # shuffles keep every cell's range, nothing was removed or re-sorted since): the
+                # stable re-sort of reset_cell_idx (impl/particle_attributes.py:86-88) would
+                # reproduce idx and cell_start as they are
+                attrs.cell_idx.reset_index()
+            else:
+                attrs.reset_cell_idx()
+            self.rnd_opt_coll.reset()
+
+        def _kernel_name(self):
+            """name of the fused kernel's instantiation for this configuration, or None when the
+            fused step does not cover it (decided without touching the particle state)"""
             part = self.particulator
             name = type(self.collision_kernel).__name__
             if isinstance(self.collision_kernel, Parameterized):
@@ -123,17 +158,27 @@ def make_fused_coalescence():
                     or getattr(part.backend.formulae.particle_shape_and_density, "__name__",
                                "LiquidSpheres") != "LiquidSpheres"):
                 return None
+            return name
+
+        def _fused_plan(self):
+            """(kernel name, a, b, caretaker of the current sort) or None"""
+            part = self.particulator
+            name = self._kernel_name()
+            if name is None:
+                return None
             cell_start = part.attributes.cell_start  # sorts by cell when needed
             facts = part.backend.sort_facts(cell_start.data)
             if facts is None or facts.max_cell > m.fused_max_cell_size():
                 return None
             return (name, *_KERNELS[name](self.collision_kernel), facts)
 
-        def step(self):
+        def step(self, want_end=False):  # pylint: disable=arguments-differ
+            """one (sub-)step.  `want_end` (adaptive loop): returns adaptive_sdm_end's result
+            when the fused launch computed it and it is still valid, else None"""
             plan = self._fused_plan()
             if plan is None:
                 super().step()
-                return
+                return None
             name, kernel_a, kernel_b, facts = plan
             part, attrs = self.particulator, self.particulator.attributes
             # the reference reaches these through the same name-mangled handles
@@ -144,7 +189,7 @@ def make_fused_coalescence():
             mass_row = keys.get("signed water mass", keys.get("water mass"))
             if mass_row is None:
                 super().step()
-                return
+                return None
             rnd = self.rnd_opt_coll.rnd
             if isinstance(rnd, Random) and not self.rnd_opt_coll.optimized_random:
                 # device Philox: generated inside the kernel
@@ -181,7 +226,8 @@ def make_fused_coalescence():
                     "dt_left": self.dt_left.data, "stats_n_substep": self.stats_n_substep.data,
                     "stats_dt_min": self.stats_dt_min.data, "dt_min": self.dt_coal_range[0],
                     "dt_max": self.dt_coal_range[1], "rank_to_cell": facts.rank_to_cell,
-                    "rank_info": self._rank_info}
+                    "rank_info": self._rank_info,
+                    "adaptive_end": self._words[1:3] if want_end else None}
             else:
                 substeps = self._Collision__substeps  # pylint: disable=no-member
             length = len(idx)
@@ -201,13 +247,24 @@ def make_fused_coalescence():
                 nf_slot=self._nf_slot, refresh_nf=self._nf_facts != sort_id, **kw)
             m.check(err, "fused_collision_step")
             self._nf_facts = sort_id
+            self._last_facts = facts
             if facts.length < idx.data.numel():  # flagged positions beyond the sorted range stay
                 facts.tmp_idx.data[facts.length:] = idx.data[facts.length:]
             idx.data, facts.tmp_idx.data = facts.tmp_idx.data, idx.data
             self.is_first_in_pair.length = length
             self.n_fused_steps += 1
             # Particulator.collision_coalescence_breakup, PySDM/particulator.py:210-213
-            attrs.sanitize()
+            end = None
+            if want_end:  # `healthy` and the next working length in one read-back
+                self._words[0:1].copy_(healthy.data)
+                self._words_host.copy_(self._words, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                if self._words_host[0]:
+                    end = int(self._words_host[1])  # (sanitize() would find nothing to do)
+                else:
+                    attrs.sanitize()  # removes the dead super-droplets; idx is re-sorted next
+            else:
+                attrs.sanitize()
             attrs.mark_updated("multiplicity")
             for key in attrs.get_extensive_attribute_keys():
                 attrs.mark_updated(key)
@@ -219,5 +276,6 @@ def make_fused_coalescence():
                     for dependency in attribute.dependencies:
                         dependency.update()
                     attribute.timestamp = sum(d.timestamp for d in attribute.dependencies)
+            return end
 
     return FusedCoalescence

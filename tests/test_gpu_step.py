@@ -108,6 +108,10 @@ CASES = {
                               adaptive=True, dt_coal_range=(0.02, 1.0), max_mult=2),
     "adaptive_big_cells": dict(seed=9, n_cell=6, mean=2500, n_attr=1, dv=3e-7, steps=3,
                                adaptive=True, dt_coal_range=(0.05, 1.0), max_mult=3),
+    # stats_dt_min reset to a finite value (as the CollisionTimestepMin product does,
+    # products/collision/collision_timestep_min.py:21-24): finished cells keep updating it
+    "adaptive_stats_reset": dict(seed=11, n_cell=150, mean=40, n_attr=1, dv=1e-8, steps=4,
+                                 adaptive=True, dt_coal_range=(0.01, 1.0), stats_reset=True),
     "adaptive_dt_min": dict(seed=10, n_cell=50, mean=30, n_attr=1, dv=2e-10, steps=2,
                             adaptive=True, dt_coal_range=(0.25, 1.0)),
 }
@@ -120,6 +124,7 @@ def test_against_oracle(case, fused):
     steps, dv = c.pop("steps"), c.pop("dv")
     substeps = c.pop("substeps", 1)
     extra = {k: c.pop(k) for k in ("adaptive", "dt_coal_range", "optimized_random") if k in c}
+    stats_reset = c.pop("stats_reset", False)
     pop = ragged_population(**c)
     if case == "one_cell":
         pop["cell_id"] = np.zeros_like(pop["cell_id"])
@@ -128,10 +133,15 @@ def test_against_oracle(case, fused):
     dev = device_sim(kernel=device_kernel(b=GOLOVIN_B), host_rng=True, fused=fused, **pop,
                      **common)
     for step in range(steps):
+        if stats_reset:
+            ora.stats_dt_min[:] = 1.0
+            dev.stats_dt_min.fill_(1.0)
         ora()
         dev()
         compare_states(dev, ora, f"{case} step {step}")
     assert ora.coalescence_rate.sum() > 0, "test population never collided"
+    if stats_reset:
+        assert np.isfinite(ora.stats_dt_min).all() and ora.stats_dt_min.min() < 1.0
     if extra.get("adaptive"):
         assert ora.stats_n_substep.max() > steps, "the time step was never cut"
         np.testing.assert_array_equal(dev.host("dt_left"), ora.dt_left)
@@ -393,12 +403,18 @@ def test_geometric_standalone_against_oracle(fused, mode):
                   "stats_n_substep"):
             np.testing.assert_array_equal(dev.host(k), getattr(ora, k), f"{what}: {k}")
         # the derived attributes the fused step maintains == a full recomputation
-        np.testing.assert_allclose(dev.host("radius")[ora.idx[:n]], ora.kernel.radius[ora.idx[:n]],
+        expect = np.empty(n_sd)
+        ora.be.product_scalar(expect, ora.volume(), 1 / ora.kernel.PI_4_3)
+        ora.be.power(expect, 1 / 3)
+        if not fused:  # the method-level path recomputes them before a step, like the orchestration
+            dev.refresh_dependents()
+        np.testing.assert_allclose(dev.host("radius")[ora.idx[:n]], expect[ora.idx[:n]],
                                    rtol=1e-14, atol=0, err_msg=what)
-        kept = dev.host("radius").copy()
+        kept = {k: dev.host(k).copy() for k in ("radius", "fall_velocity", "_volume")}
         dev.refresh_dependents()
-        np.testing.assert_array_equal(dev.host("radius").view(np.int64), kept.view(np.int64),
-                                      f"{what}: radius kept current by the step != recomputed")
+        for k, v in kept.items():
+            np.testing.assert_array_equal(dev.host(k).view(np.int64), v.view(np.int64),
+                                          f"{what}: {k} kept current by the step != recomputed")
     assert ora.coalescence_rate.sum() > 0
     if mode != "fixed":
         assert ora.stats_n_substep.max() > 4, "the time step was never cut"

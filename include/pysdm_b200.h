@@ -249,9 +249,19 @@ typedef struct pysdm_b200_fused_args {
     double dep_table_factor, dep_radius_max;      /* Interpolation.factor, .maximum_radius */
     int64_t *dep_status;         /* [1]: set to 1 if a refreshed radius exceeds dep_radius_max (the
                                     reference raises ValueError at the next recalculation) */
+    /* ---- cells larger than pysdm_b200_fused_max_cell_size() (single-cell boxes: BASELINE
+     * configs[0..2]): the step runs as the parallel replay of the cells' serial shuffle chains
+     * (pysdm_b200_shuffle_local) followed by one streaming kernel over the pair slots (two for the
+     * adaptive time step), all inside the one call; needs device scratch */
+    void *ws;                    /* scratch of >= pysdm_b200_fused_workspace_bytes(n_sd, n_cell)
+                                    bytes, or NULL: large cells are then refused as before */
+    uint64_t ws_bytes;
+    int64_t sorted_length;       /* cell_start[n_cell] when the working length was cut below it
+                                    (adaptive loop); 0 = `length` */
 } pysdm_b200_fused_args;
 
 int64_t pysdm_b200_fused_max_cell_size(void);
+size_t pysdm_b200_fused_workspace_bytes(int64_t n_sd, int64_t n_cell);
 /* shuffle_local (index_methods.py:32-44) for populations whose cells all hold at most
  * max_cell_size <= pysdm_b200_fused_max_cell_size() super-droplets: the staging + swap-chain
  * phases of the fused step alone (shared memory, one launch) instead of the general

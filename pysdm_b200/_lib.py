@@ -53,6 +53,7 @@ SIGNATURES = {
     "pysdm_b200_mass_of_water_volume": (INT, (P, P, I64, F64, P)),
     "pysdm_b200_max_cell_size": (INT, (P, I64, P, P, P)),
     "pysdm_b200_fused_max_cell_size": (I64, ()),
+    "pysdm_b200_fused_workspace_bytes": (SIZE, (I64, I64)),
     "pysdm_b200_fused_collision_step": (INT, (P, P)),
     "pysdm_b200_shuffle_local_batched": (INT, (P, P, P, I64, I64, I64, P, P)),
     "pysdm_b200_invert_index": (INT, (P, P, I64, P)),
@@ -111,7 +112,8 @@ class FusedArgs(ctypes.Structure):
            ("adaptive_end", P), ("length_dev", P),
            ("dep_volume", P), ("dep_radius", P), ("dep_velocity", P), ("dep_table_b", P),
            ("dep_table_c", P), ("dep_radius_scale", F64), ("dep_radius_exponent", F64),
-           ("dep_table_factor", F64), ("dep_radius_max", F64), ("dep_status", P)])
+           ("dep_table_factor", F64), ("dep_radius_max", F64), ("dep_status", P),
+           ("ws", P), ("ws_bytes", U64), ("sorted_length", I64)])
 
 
 KERNELS = {"Golovin": 0, "ConstantK": 1, "Linear": 2, "Geometric": 3, "Hydrodynamic": 4}

@@ -350,10 +350,9 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.get_cell_start()
         if self.max_cell is None:
             self.max_cell = m.max_cell_size(self.cell_start)
-        ok = self.max_cell <= m.fused_max_cell_size()
-        if not ok and self.fused is True:
-            raise RuntimeError(f"fused step refused: a cell holds {self.max_cell} super-droplets")
-        return ok
+        # (cells beyond m.fused_max_cell_size() -- boxes -- take the shuffle replay + streaming
+        # kernel inside the same entry point, csrc/stream.cu)
+        return self.n_sd < 2 ** 31
 
     def step(self):
         if self._fused_ok():
@@ -449,7 +448,8 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             norm_factor=self.norm_factor, collision_rate=self.collision_rate,
             collision_rate_deficit=self.collision_rate_deficit,
             coalescence_rate=self.coalescence_rate, healthy=self.healthy, status=self.status,
-            length=self.length, max_cell=self.max_cell, kernel=self.kernel.fused,
+            length=self.length, sorted_length=self.sorted_length, max_cell=self.max_cell,
+            kernel=self.kernel.fused,
             kernel_a=self.kernel.a, kernel_b=self.kernel.b, timestep=self.dt, dv=self.dv,
             rho_w=self.rho_w, substeps=1 if self.adaptive else self.substeps,
             nf_slot=self.nf_slot, refresh_nf=not self.nf_valid, gate=self.gate if gated else None,

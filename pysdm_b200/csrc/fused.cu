@@ -92,6 +92,14 @@ PYSDM_EXPORT int pysdm_b200_dependent_attributes(const double *mass, i64 n, doub
 
 PYSDM_EXPORT int64_t pysdm_b200_fused_max_cell_size(void) { return kCtaPos; }
 
+// stream.cu: the step for cells beyond kCtaPos (boxes)
+int pysdm_stream_collision_step(const FusedArgs &a, cudaStream_t st);
+size_t pysdm_stream_ws_bytes(i64 n_sd, i64 n_cell);
+PYSDM_EXPORT size_t pysdm_b200_fused_workspace_bytes(int64_t n_sd, int64_t n_cell)
+{
+    return pysdm_stream_ws_bytes(n_sd, n_cell);
+}
+
 // precondition of div_by(): b normal, moderate, significand not all ones
 static bool divisor_ok(double b)
 {
@@ -116,14 +124,17 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
 {
     FusedArgs a = *host_args;
     if (a.n_sd <= 0 || a.n_sd >= ((i64)1 << 32) || a.n_cell <= 0) return (int)cudaErrorInvalidValue;
-    if (a.max_cell_size > kCtaPos) return (int)cudaErrorInvalidConfiguration;
+    const bool big = a.max_cell_size > kCtaPos;  // -> stream.cu (needs scratch)
+    if (big && a.ws == nullptr) return (int)cudaErrorInvalidConfiguration;
     if ((a.u01 == nullptr) != (a.rand == nullptr)) return (int)cudaErrorInvalidValue;
     cudaStream_t st = (cudaStream_t)stream;
     if (a.nf_slot == nullptr) return (int)cudaErrorInvalidValue;
     const bool adaptive = a.adaptive != 0;
     if (adaptive) {
-        if (!a.dt_left || !a.stats_n_substep || !a.stats_dt_min || !a.rank_to_cell || !a.rank_info ||
-            !(a.dt_min >= 0.0) || !(a.timestep > 0.0))
+        if (big) a.rank_info = nullptr;  // (cell ids come from cell_id[] there)
+        if (!a.dt_left || !a.stats_n_substep || !a.stats_dt_min ||
+            (!big && (!a.rank_to_cell || !a.rank_info)) || !(a.dt_min >= 0.0) ||
+            !(a.timestep > 0.0))
             return (int)cudaErrorInvalidValue;
         a.substeps = 1.0;
         a.refresh_nf = 1;  // cell_idx was re-sorted since the previous sub-step
@@ -147,6 +158,12 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
     for (int r = 0; r < 10; ++r) {  // Philox4x32 key schedule (philox.cuh)
         a.philox_round_keys[2 * r] = (u32)a.seed + (u32)r * 0x9E3779B9u;
         a.philox_round_keys[2 * r + 1] = (u32)(a.seed >> 32) + (u32)r * 0xBB67AE85u;
+    }
+    if (big) {
+        if ((a.kernel == KERNEL_GEOMETRIC || a.kernel == KERNEL_HYDRODYNAMIC) &&
+            (a.radius == nullptr || a.fall_velocity == nullptr))
+            return (int)cudaErrorInvalidValue;
+        return pysdm_stream_collision_step(a, st);
     }
     const i64 n_batches = (a.n_cell + cpb - 1) / cpb;
     const bool philox = a.u01 == nullptr;

@@ -206,13 +206,93 @@ __device__ __forceinline__ void counter_add(i64 *counters, i64 cid, i64 value, b
 // tells whether this lane holds an entry: pf = local position of the pair's first member,
 // g_raw = ceil(prob - rand) != 0.  The pair is re-read from shared memory and re-sorted by
 // multiplicity (cheap, cached) instead of being carried through the queue.
+// ---- one colliding pair: gamma cap, coalescence, derived attributes ----------------------------
+// (compute_gamma :546-558 and collision_coalescence/coalesce :44-59,:418-477 of
+// impl_numba/methods/collisions_methods.py).  (sj, sk) sorted by multiplicity (n_j >= n_k),
+// g_raw = ceil(prob - rand) != 0; *gamma_slot is rewritten when the cap n_j // n_k applies.
+// Returns the three counter increments.
+struct HitResult {
+    i64 add_rate, add_deficit, add_coal;
+};
+template <int K>
+__device__ __forceinline__ HitResult hit_pair(const FusedArgs &a, u32 sj, u32 sk, i64 n_j, i64 n_k,
+                                              double g_raw, double *gamma_slot)
+{
+    HitResult r = {0, 0, 0};
+    // g = min(int(gamma), n_j // n_k); n_j >= n_k > 0 here, so int(gamma) <= 1 needs no division
+    const i64 gi = f64_to_i64(g_raw);
+    i64 g = gi;
+    if (gi > 1 || n_k <= 0) {
+        const i64 prop = floordiv(n_j, n_k);
+        g = gi < prop ? gi : prop;
+    }
+    const double gamma = i64_to_f64(g);
+    if (g != gi) *gamma_slot = gamma;
+    r.add_rate = g * n_k;
+    r.add_deficit = (gi - g) * n_k;
+    if (gamma != 0.0) {
+        // coalesce: float arithmetic stored to int64 (quirk A7), attribute update fused (fma)
+        const double f_nj = i64_to_f64(n_j), f_nk = i64_to_f64(n_k);
+        const double gnk = gamma * f_nk;
+        r.add_coal = f64_to_i64(gnk);
+        const double new_n = f_nj - gnk;
+        i64 nj_new, nk_new = n_k;
+        const bool keep = new_n > 0;
+        if (keep) {
+            nj_new = f64_to_i64(new_n);
+            a.multiplicity[sj] = nj_new;
+        } else {
+            nj_new = n_k >> 1;  // n_k // 2 (floor, also for negatives)
+            nk_new = n_k - nj_new;
+            a.multiplicity[sj] = nj_new;
+            a.multiplicity[sk] = nk_new;
+        }
+        double new_mass = 0.0;
+        for (i64 r_ = 0; r_ < a.n_attr; ++r_) {
+            double *row = a.attributes + r_ * a.n_sd;
+            const double v = fma(gamma, row[sj], row[sk]);
+            row[sk] = v;
+            if (!keep) row[sj] = v;
+            if (r_ == a.mass_row) new_mass = v;
+        }
+        if ((K == KERNEL_GEOMETRIC || K == KERNEL_HYDRODYNAMIC) && a.dep_radius != nullptr) {
+            // the attributes derived from the water mass, for the changed super-droplets only
+            DependentParams dp;
+            dp.rho_w = a.rho_w;
+            dp.radius_scale = a.dep_radius_scale;
+            dp.radius_exponent = a.dep_radius_exponent;
+            dp.table_factor = a.dep_table_factor;
+            dp.radius_max = a.dep_radius_max;
+            dp.table_b = a.dep_table_b;
+            dp.table_c = a.dep_table_c;
+            double vol, rad, vel;
+            const bool ok = dependents_of(new_mass, dp, vol, rad, vel);
+            if (!ok && a.dep_status != nullptr) a.dep_status[0] = 1;
+            if (a.dep_volume != nullptr) a.dep_volume[sk] = vol;
+            a.dep_radius[sk] = rad;
+            if (ok && a.dep_velocity != nullptr) a.dep_velocity[sk] = vel;
+            if (!keep) {
+                if (a.dep_volume != nullptr) a.dep_volume[sj] = vol;
+                a.dep_radius[sj] = rad;
+                if (ok && a.dep_velocity != nullptr) a.dep_velocity[sj] = vel;
+            }
+        }
+        if (nj_new == 0 || nk_new == 0) {
+            a.healthy[0] = 0;
+            if (a.gate) a.gate[0] = a.epoch;
+        }
+    }
+    return r;
+}
+
 template <int K, bool kAggregate, bool kAdaptive>
 __device__ __forceinline__ void process_hits(const FusedArgs &a, u32 pf, double g_raw, bool mine,
                                              const u32 *sd, const u8 *cellof, u32 cell_mask,
                                              const i64 *cidv, double *gamma_b)
 {
     bool active = false;
-    i64 cid = 0, add_rate = 0, add_deficit = 0, add_coal = 0;
+    i64 cid = 0;
+    HitResult r = {0, 0, 0};
     if (mine) {
         u32 sj = sd[phys((int)pf)], sk = sd[phys((int)pf + 1)];
         i64 n_j = a.multiplicity[sj], n_k = a.multiplicity[sk];
@@ -220,76 +300,14 @@ __device__ __forceinline__ void process_hits(const FusedArgs &a, u32 pf, double 
             const u32 t = sj; sj = sk; sk = t;
             const i64 tn = n_j; n_j = n_k; n_k = tn;
         }
-        // g = min(int(gamma), n_j // n_k); n_j >= n_k > 0 here, so int(gamma) <= 1 needs no division
-        const i64 gi = f64_to_i64(g_raw);
-        i64 g = gi;
-        if (gi > 1 || n_k <= 0) {
-            const i64 prop = floordiv(n_j, n_k);
-            g = gi < prop ? gi : prop;
-        }
-        const double gamma = i64_to_f64(g);
-        if (g != gi) gamma_b[pf >> 1] = gamma;
         cid = cidv[cellof[pf] & cell_mask];
         if (kAdaptive) cid &= kCidMask;
-        add_rate = g * n_k;
-        add_deficit = (gi - g) * n_k;
         active = true;
-        if (gamma != 0.0) {
-            // coalesce: float arithmetic stored to int64 (quirk A7), attribute update fused (fma)
-            const double f_nj = i64_to_f64(n_j), f_nk = i64_to_f64(n_k);
-            const double gnk = gamma * f_nk;
-            add_coal = f64_to_i64(gnk);
-            const double new_n = f_nj - gnk;
-            i64 nj_new, nk_new = n_k;
-            const bool keep = new_n > 0;
-            if (keep) {
-                nj_new = f64_to_i64(new_n);
-                a.multiplicity[sj] = nj_new;
-            } else {
-                nj_new = n_k >> 1;  // n_k // 2 (floor, also for negatives)
-                nk_new = n_k - nj_new;
-                a.multiplicity[sj] = nj_new;
-                a.multiplicity[sk] = nk_new;
-            }
-            double new_mass = 0.0;
-            for (i64 r_ = 0; r_ < a.n_attr; ++r_) {
-                double *row = a.attributes + r_ * a.n_sd;
-                const double v = fma(gamma, row[sj], row[sk]);
-                row[sk] = v;
-                if (!keep) row[sj] = v;
-                if (r_ == a.mass_row) new_mass = v;
-            }
-            if ((K == KERNEL_GEOMETRIC || K == KERNEL_HYDRODYNAMIC) && a.dep_radius != nullptr) {
-                // the attributes derived from the water mass, for the changed super-droplets only
-                DependentParams dp;
-                dp.rho_w = a.rho_w;
-                dp.radius_scale = a.dep_radius_scale;
-                dp.radius_exponent = a.dep_radius_exponent;
-                dp.table_factor = a.dep_table_factor;
-                dp.radius_max = a.dep_radius_max;
-                dp.table_b = a.dep_table_b;
-                dp.table_c = a.dep_table_c;
-                double vol, rad, vel;
-                const bool ok = dependents_of(new_mass, dp, vol, rad, vel);
-                if (!ok && a.dep_status != nullptr) a.dep_status[0] = 1;
-                if (a.dep_volume != nullptr) a.dep_volume[sk] = vol;
-                a.dep_radius[sk] = rad;
-                if (ok && a.dep_velocity != nullptr) a.dep_velocity[sk] = vel;
-                if (!keep) {
-                    if (a.dep_volume != nullptr) a.dep_volume[sj] = vol;
-                    a.dep_radius[sj] = rad;
-                    if (ok && a.dep_velocity != nullptr) a.dep_velocity[sj] = vel;
-                }
-            }
-            if (nj_new == 0 || nk_new == 0) {
-                a.healthy[0] = 0;
-                if (a.gate) a.gate[0] = a.epoch;
-            }
-        }
+        r = hit_pair<K>(a, sj, sk, n_j, n_k, g_raw, gamma_b + (pf >> 1));
     }
-    counter_add<kAggregate>(a.collision_rate, cid, add_rate, active);
-    counter_add<kAggregate>(a.collision_rate_deficit, cid, add_deficit, active);
-    counter_add<kAggregate>(a.coalescence_rate, cid, add_coal, active);
+    counter_add<kAggregate>(a.collision_rate, cid, r.add_rate, active);
+    counter_add<kAggregate>(a.collision_rate_deficit, cid, r.add_deficit, active);
+    counter_add<kAggregate>(a.coalescence_rate, cid, r.add_coal, active);
 }
 
 // ---- adaptive time step helpers ------------------------------------------------------------

@@ -162,6 +162,40 @@ static int shuffle_impl(i64 *idx, const double *u01, const i64 *cell_start, i64 
 
 PYSDM_EXPORT size_t pysdm_b200_shuffle_workspace_bytes(i64 length) { return shuffle_ws_bytes(length); }
 
+// shuffle_local out of place (idx_out != idx_in): what the streaming collision step (stream.cu)
+// starts with; same kernels as above without the copy back.  Workspace: shuffle_ws_bytes(length).
+int pysdm_shuffle_local_to(const i64 *idx_in, i64 *idx_out, const double *u01,
+                           const i64 *cell_start, i64 n_cell, i64 length, void *ws,
+                           size_t ws_bytes, cudaStream_t st)
+{
+    if (length <= 0) return 0;
+    const int g = grid_for(length);
+    if (length < 2) {
+        k_copy_i64<<<g, kThreads, 0, st>>>(idx_out, idx_in, length);
+        return LAUNCH_CHECK();
+    }
+    if (length >= ((i64)1 << 31)) return (int)cudaErrorInvalidValue;
+    if (ws_bytes < shuffle_ws_bytes(length)) return (int)cudaErrorMemoryAllocation;
+    char *w = (char *)ws;
+    i32 *tgt = (i32 *)w;
+    w += align_up(sizeof(i32) * (size_t)length);
+    u32 *cnt = (u32 *)w;
+    w += align_up(sizeof(u32) * (size_t)(length + 1));
+    u32 *fill = (u32 *)w;
+    w += align_up(sizeof(u32) * (size_t)length);
+    i32 *list = (i32 *)w;
+    w += align_up(sizeof(i32) * (size_t)length);
+    w += align_up(sizeof(i64) * (size_t)length);  // (the in-place variant's output buffer)
+    u32 *scan_ws = (u32 *)w;
+    cudaMemsetAsync(cnt, 0, (size_t)((char *)list - (char *)cnt), st);
+    k_shuffle_targets<true><<<g, kThreads, 0, st>>>(u01, cell_start, n_cell, length, tgt, cnt);
+    device_exclusive_scan<u32>(cnt, cnt, length, 1, scan_ws, st);
+    k_shuffle_fill<<<g, kThreads, 0, st>>>(tgt, cnt, fill, list, length);
+    k_shuffle_walk<<<g, kThreads, 0, st>>>(idx_in, idx_out, tgt, cnt, list, length);
+    return LAUNCH_CHECK();
+}
+size_t pysdm_shuffle_ws_bytes(i64 length) { return shuffle_ws_bytes(length); }
+
 PYSDM_EXPORT int pysdm_b200_shuffle_global(i64 *idx, i64 length, const double *u01, void *ws,
                                            size_t ws_bytes, void *stream)
 {

@@ -168,7 +168,7 @@ def make_fused_coalescence():
                 return None
             cell_start = part.attributes.cell_start  # sorts by cell when needed
             facts = part.backend.sort_facts(cell_start.data)
-            if facts is None or facts.max_cell > m.fused_max_cell_size():
+            if facts is None or part.n_sd >= 2 ** 31:
                 return None
             return (name, *_KERNELS[name](self.collision_kernel), facts)
 
@@ -241,7 +241,8 @@ def make_fused_coalescence():
                 norm_factor=self.norm_factor_temp.data, collision_rate=self.collision_rate.data,
                 collision_rate_deficit=self.collision_rate_deficit.data,
                 coalescence_rate=self.coalescence_rate.data, healthy=healthy.data,
-                status=self._status, length=length, max_cell=facts.max_cell, kernel=name,
+                status=self._status, length=length, sorted_length=facts.length,
+                max_cell=facts.max_cell, kernel=name,
                 kernel_a=kernel_a, kernel_b=kernel_b, timestep=part.dt, dv=part.mesh.dv,
                 rho_w=part.backend.rho_w, substeps=substeps, mass_row=mass_row,
                 nf_slot=self._nf_slot, refresh_nf=self._nf_facts != sort_id, **kw)

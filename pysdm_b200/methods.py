@@ -266,7 +266,7 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
                          substeps=1, mass_row=0, u01=None, rand=None, seed=0, call_u01=0,
                          call_rand=0, nf_slot, refresh_nf=True, gate=None, epoch=1, radius=None,
                          fall_velocity=None, berry_params=None, berry_unit=1.0, adaptive=None,
-                         dependents=None):
+                         dependents=None, sorted_length=0):
     """one Collision.step() in one launch; returns the CUDA error code (9 = a cell is
     larger than the fused path supports -> use the method-level functions).  kernel
     "Geometric": kernel_a = PI * collection_efficiency, `radius` and `fall_velocity` = the
@@ -291,14 +291,19 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         kernel_b=float(kernel_b), kernel=_lib.KERNELS[kernel], reserved=0,
         max_cell_size=int(max_cell), nf_slot=_pf(nf_slot), refresh_nf=int(bool(refresh_nf)),
         gate=_pi(gate), epoch=int(epoch), radius=_pf(radius), fall_velocity=_pf(fall_velocity))
+    if int(max_cell) > fused_max_cell_size():  # boxes: shuffle replay + streaming kernel(s)
+        nbytes = _lib.load().pysdm_b200_fused_workspace_bytes(n_sd, cell_start.numel() - 1)
+        ws = WS.dev("fused_stream", nbytes, idx_in.device)
+        args.ws, args.ws_bytes = _p(ws), ws.numel()
+    args.sorted_length = int(sorted_length)
     if adaptive is not None:
         args.adaptive = 1
         args.dt_left = _pf(adaptive["dt_left"])
         args.stats_n_substep = _pi(adaptive["stats_n_substep"])
         args.stats_dt_min = _pf(adaptive["stats_dt_min"])
         args.dt_min, args.dt_max = float(adaptive["dt_min"]), float(adaptive["dt_max"])
-        args.rank_to_cell = _pi(adaptive["rank_to_cell"])
-        args.rank_info = _pi(adaptive["rank_info"])
+        args.rank_to_cell = _pi(adaptive.get("rank_to_cell"))
+        args.rank_info = _pi(adaptive.get("rank_info"))
         args.adaptive_end = _pi(adaptive.get("adaptive_end"))
         args.length_dev = _pi(adaptive.get("length_dev"))
     if dependents is not None:  # see pysdm_b200_fused_args `dep_*`

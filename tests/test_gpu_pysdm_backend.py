@@ -93,6 +93,10 @@ CASES = {
                              kw=dict(adaptive=True, dt_coal_range=(0.05, 1.0),
                                      optimized_random=True)),
     "box": dict(grid=(1,), n_sd=1024, dv=1e-7, kw=dict(adaptive=False)),
+    # one cell beyond the shared-memory batches of the fused step: shuffle replay + streaming kernel
+    "box_stream": dict(grid=(1,), n_sd=20000, dv=2e-5, kw=dict(adaptive=False)),
+    "box_stream_adaptive": dict(grid=(1,), n_sd=20000, dv=4e-6,
+                                kw=dict(adaptive=True, dt_coal_range=(0.02, 1.0))),
 }
 
 
@@ -138,7 +142,7 @@ def test_b200_backend_equals_numba_backend(pysdm, case):
 
 @pytest.mark.parametrize("host_rng", (True, False))
 @pytest.mark.parametrize("case", ("local", "substeps", "box", "global", "adaptive",
-                                  "adaptive_optrand"))
+                                  "adaptive_optrand", "box_stream", "box_stream_adaptive"))
 def test_fused_coalescence_dynamic(pysdm, case, host_rng):
     """`pysdm_b200.FusedCoalescence` (PySDM's Coalescence with step() on the one-launch fused
     kernel) inside the unmodified PySDM orchestration.  host_rng=True: against the reference's

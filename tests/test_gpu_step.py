@@ -96,6 +96,16 @@ CASES = {
     "big_cells": dict(seed=3, n_cell=5, mean=3000, n_attr=1, dv=2e-5, steps=3),
     "substeps": dict(seed=4, n_cell=64, mean=40, n_attr=2, dv=1e-7, steps=4, substeps=3),
     "one_cell": dict(seed=5, n_cell=1, mean=5000, n_attr=1, dv=2e-6, steps=3),
+    # cells beyond the shared-memory batches (> 8192 SDs; boxes): shuffle replay + streaming kernel
+    "box_stream": dict(seed=12, n_cell=1, mean=20000, n_attr=2, dv=3e-5, steps=3),
+    "big_cells_stream": dict(seed=13, n_cell=6, mean=11000, n_attr=1, dv=2e-5, steps=3),
+    "box_stream_substeps": dict(seed=14, n_cell=1, mean=9000, n_attr=1, dv=1e-5, steps=2,
+                                substeps=2),
+    "adaptive_box_stream": dict(seed=15, n_cell=1, mean=20000, n_attr=1, dv=3e-6, steps=3,
+                                adaptive=True, dt_coal_range=(0.02, 1.0)),
+    "adaptive_big_stream": dict(seed=16, n_cell=6, mean=11000, n_attr=2, dv=2e-6, steps=3,
+                                adaptive=True, dt_coal_range=(0.05, 1.0), optimized_random=True,
+                                max_mult=2),
     # adaptive time step (one fused launch per sub-step): ragged cells so that the re-sorted
     # cell_idx shifts the pair parity (quirk A2) and `normalize` picks other cells' factors (A1)
     "adaptive_ragged": dict(seed=6, n_cell=300, mean=40, n_attr=3, dv=1e-8, steps=4,
@@ -126,7 +136,7 @@ def test_against_oracle(case, fused):
     extra = {k: c.pop(k) for k in ("adaptive", "dt_coal_range", "optimized_random") if k in c}
     stats_reset = c.pop("stats_reset", False)
     pop = ragged_population(**c)
-    if case == "one_cell":
+    if c["n_cell"] == 1:
         pop["cell_id"] = np.zeros_like(pop["cell_id"])
     common = dict(dt=1.0, dv=dv, seed=100 + c["seed"], substeps=substeps, **extra)
     ora = OracleCollision(kernel=OGolovin(GOLOVIN_B), **pop, **common)
@@ -352,9 +362,10 @@ class _Host:  # pylint: disable=too-few-public-methods
         return self.sim.host(name)
 
 
+@pytest.mark.parametrize("n_cell", (96, 1))
 @pytest.mark.parametrize("mode", ("fixed", "adaptive_optrand"))
 @pytest.mark.parametrize("fused", (True, False))
-def test_geometric_standalone_against_oracle(fused, mode):
+def test_geometric_standalone_against_oracle(fused, mode, n_cell):
     """BASELINE configs[3] in kind without PySDM in the process: `DeviceCollision` with the
     Geometric kernel (radius and Gunn-Kinzer fall velocity derived from the water mass; the
     fused step refreshes them only for the super-droplets a coalescence changed, the
@@ -368,8 +379,7 @@ def test_geometric_standalone_against_oracle(fused, mode):
     table = np.load(os.path.join(os.path.dirname(__file__), "..", "pysdm_b200", "data",
                                  "gunn_kinzer_1949.npz"))
     rng = np.random.default_rng(31)
-    n_cell = 96
-    sizes = rng.poisson(128, n_cell)
+    sizes = rng.poisson(12288 // n_cell, n_cell)  # one cell: beyond the shared-memory batches
     cell_id = np.repeat(np.arange(n_cell), sizes)
     n_sd = len(cell_id)
     radius = 10e-6 * np.exp(0.47 * rng.standard_normal(n_sd))
@@ -379,7 +389,8 @@ def test_geometric_standalone_against_oracle(fused, mode):
     pop = {"multiplicity": rng.integers(1, 2 * int(100e6 * dv / 128), n_sd).astype(np.int64),
            "water_mass": 1000.0 * volume, "cell_id": cell_id, "n_cell": n_cell,
            "extra_attributes": [volume * 1e-3, volume * 0.6e-3]}
-    common = dict(dt=5.0, dv=dv, seed=77)
+    # (one cell of 12288: every droplet meets ~96 times more partners; same droplets, 96 x the volume)
+    common = dict(dt=5.0, dv=dv * (1 if n_cell > 1 else 96), seed=77)
     if mode == "adaptive_optrand":
         common.update(adaptive=True, optimized_random=True, dt_coal_range=(0.1, 5.0))
     ora = OracleCollision(kernel=OGeometric(1.0, (table["a"], table["b"], float(table["factor"]),

@@ -258,6 +258,8 @@ typedef struct pysdm_b200_fused_args {
     uint64_t ws_bytes;
     int64_t sorted_length;       /* cell_start[n_cell] when the working length was cut below it
                                     (adaptive loop); 0 = `length` */
+    int64_t skip_coalescence;    /* != 0: stop after compute_gamma (breakup: pysdm_b200_fused_breakup
+                                    takes over) */
 } pysdm_b200_fused_args;
 
 int64_t pysdm_b200_fused_max_cell_size(void);
@@ -270,6 +272,58 @@ int pysdm_b200_shuffle_local_batched(int64_t *idx, const double *u01, const int6
                                      int64_t n_cell, int64_t n_sd, int64_t max_cell_size,
                                      int64_t *status, void *stream);
 int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *host_args, void *stream);
+
+/* ---- fused breakup: the second half of a Collision.step() with enable_breakup ---------------
+ * (PySDM/dynamics/collisions/collision.py:206-234).  pysdm_b200_fused_collision_step with
+ * skip_coalescence != 0 runs the step up to and including compute_gamma; this entry point then
+ * handles, in ONE launch over the pair slots with gamma != 0: the coalescence efficiency
+ * (ConstEc, Straub2010Ec: coalescence_efficiencies/straub2010.py:24-47 -- a chain of ~15
+ * pairwise Storage operations in the reference --, or a Parameterized one such as Berry1967:
+ * _parameterized.py:16-24), the breakup efficiency (ConstEb), the fragment mass (AlwaysN:
+ * breakup_fragmentations/always_n.py:12-15; Straub2010Nf: straub2010.py:44-102 +
+ * fragmentation_methods.py:218-260, another ~30 operations, + volume_based.py:15-17), the
+ * uniforms of the two RandomGeneratorOptimizerNoPair streams, and collision_coalescence_breakup
+ * itself (collisions_methods.py:246-311).  The operation sequences are the reference's. */
+typedef struct pysdm_b200_breakup_args {
+    int64_t *multiplicity;        /* [n_sd] */
+    const int64_t *idx;           /* [n_sd] pairs as sort_within_pair_by_attr left them */
+    double *attributes;           /* [n_attr, n_sd] */
+    const double *gamma;          /* [n_sd / 2] after compute_gamma */
+    const uint8_t *is_first_in_pair; /* [n_sd] */
+    const int64_t *cell_id;       /* [n_sd] */
+    int64_t *healthy;             /* [1] */
+    int64_t *coalescence_rate, *breakup_rate, *breakup_rate_deficit; /* [n_cell] */
+    int64_t *n_overflow;          /* [1] or NULL: counts pairs that hit max_multiplicity */
+    int64_t length, n_sd, n_attr, mass_row;
+    const double *rand_proc, *rand_frag; /* [n_sd / 2] each, or NULL = Philox (seed, call_*) */
+    uint64_t seed, call_proc, call_frag;
+    const double *volume, *radius, *fall_velocity; /* [n_sd] derived attributes (Straub, Berry) */
+    int32_t ec_kind;              /* 0 ConstEc, 1 Straub2010Ec, 2 Parameterized (linear_collection_efficiency ** 2) */
+    int32_t nf_kind;              /* 0 AlwaysN, 1 Straub2010Nf */
+    double ec_const, eb_const, nf_n;
+    double ec_params[13];         /* ec_kind 2, as in pysdm_b200_linear_collection_efficiency */
+    int64_t ec_int_mask;
+    double ec_unit;
+    double vmin, nfmax;           /* fragmentation_limiters */
+    int32_t has_nfmax, handle_all_breakups;
+    double max_multiplicity;
+    /* constants as the host's Formulae carries them (products are formed on the host exactly as
+     * the reference's Python does) */
+    double rho_w;                 /* const.rho_w */
+    double six_over_pi;           /* 6 / const.PI */
+    double pi_sgm_w;              /* const.PI * const.sgm_w */
+    double two_thirds;            /* 2 / 3 */
+    double nf_sc_factor;          /* const.PI * const.sgm_w * (6 / const.PI) ** (2 / 3) */
+    double half_rho_w;            /* const.rho_w / 2 */
+    double micro_joule;           /* si.uJ */
+    /* derived attributes kept current for the super-droplets the launch changed (as dep_* of
+     * pysdm_b200_fused_args); dep_radius == NULL: left to the caller */
+    double *dep_volume, *dep_radius, *dep_velocity;
+    const double *dep_table_b, *dep_table_c;
+    double dep_radius_scale, dep_radius_exponent, dep_table_factor, dep_radius_max;
+    int64_t *dep_status;
+} pysdm_b200_breakup_args;
+int pysdm_b200_fused_breakup(const pysdm_b200_breakup_args *host_args, void *stream);
 /* out[in[c]] = c for c < n: the rank -> cell map (`rank_to_cell` above) of the cell -> rank map
  * `cell_idx` a sort by cell has just used (collisions_methods.py:692-697 consume it that way) */
 int pysdm_b200_invert_index(int64_t *out, const int64_t *in, int64_t n, void *stream);

@@ -31,7 +31,7 @@ np.NaN = np.nan
 def dynamics(config, fused=False):
     from PySDM.dynamics import Coalescence, Collision
     if fused:
-        from pysdm_b200 import FusedCoalescence as Coalescence
+        from pysdm_b200 import FusedCoalescence as Coalescence, FusedCollision as Collision
     from PySDM.dynamics.collisions.breakup_efficiencies import ConstEb
     from PySDM.dynamics.collisions.breakup_fragmentations import Straub2010Nf
     from PySDM.dynamics.collisions.coalescence_efficiencies import Straub2010Ec
@@ -219,8 +219,7 @@ def all_configs(steps, peak_gbs, numba=True, cpu_log2=20):
     to each on a bounded sample (2^cpu_log2 SDs at most; SD-steps/s is size-normalised)"""
     rows = []
     for config in (0, 1, 2, 3):
-        fused = config != 2  # breakup runs on the method-level kernels
-        row = run(config, "B200F" if fused else "B200", steps, peak_gbs=peak_gbs)
+        row = run(config, "B200F", steps, peak_gbs=peak_gbs)
         row["baseline_config"] = f"configs[{config}]"
         if numba:
             try:

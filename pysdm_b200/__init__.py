@@ -7,7 +7,7 @@ The CUDA library (libpysdm_b200.so, built in-tree by `python -m pysdm_b200.build
 mandatory: there is no CPU fallback.
 """
 
-__all__ = ("B200", "FusedCoalescence")
+__all__ = ("B200", "FusedCoalescence", "FusedCollision")
 
 
 def __getattr__(name):  # lazy: importing the package must not need torch/CUDA (or PySDM)
@@ -15,10 +15,10 @@ def __getattr__(name):  # lazy: importing the package must not need torch/CUDA (
         from .backend import B200  # pylint: disable=import-outside-toplevel
 
         return B200
-    if name == "FusedCoalescence":  # PySDM's Coalescence with step() on the fused kernel
+    if name in ("FusedCoalescence", "FusedCollision"):  # PySDM's dynamics on the fused kernels
         from .dynamics import make_fused_coalescence  # pylint: disable=import-outside-toplevel
 
-        cls = make_fused_coalescence()
+        cls = make_fused_coalescence(name)
         globals()[name] = cls
         return cls
     raise AttributeError(name)

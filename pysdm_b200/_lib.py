@@ -55,6 +55,7 @@ SIGNATURES = {
     "pysdm_b200_fused_max_cell_size": (I64, ()),
     "pysdm_b200_fused_workspace_bytes": (SIZE, (I64, I64)),
     "pysdm_b200_fused_collision_step": (INT, (P, P)),
+    "pysdm_b200_fused_breakup": (INT, (P, P)),
     "pysdm_b200_shuffle_local_batched": (INT, (P, P, P, I64, I64, I64, P, P)),
     "pysdm_b200_invert_index": (INT, (P, P, I64, P)),
     "pysdm_b200_dependent_attributes": (INT, (P, I64, F64, F64, F64, F64, F64, P, P, P, P, P, P, P)),
@@ -113,7 +114,28 @@ class FusedArgs(ctypes.Structure):
            ("dep_volume", P), ("dep_radius", P), ("dep_velocity", P), ("dep_table_b", P),
            ("dep_table_c", P), ("dep_radius_scale", F64), ("dep_radius_exponent", F64),
            ("dep_table_factor", F64), ("dep_radius_max", F64), ("dep_status", P),
-           ("ws", P), ("ws_bytes", U64), ("sorted_length", I64)])
+           ("ws", P), ("ws_bytes", U64), ("sorted_length", I64), ("skip_coalescence", I64)])
+
+
+class BreakupArgs(ctypes.Structure):
+    """mirror of pysdm_b200_breakup_args (include/pysdm_b200.h)"""
+    _fields_ = ([(n, P) for n in (
+        "multiplicity", "idx", "attributes", "gamma", "is_first_in_pair", "cell_id", "healthy",
+        "coalescence_rate", "breakup_rate", "breakup_rate_deficit", "n_overflow")]
+        + [(n, I64) for n in ("length", "n_sd", "n_attr", "mass_row")]
+        + [("rand_proc", P), ("rand_frag", P)]
+        + [(n, U64) for n in ("seed", "call_proc", "call_frag")]
+        + [("volume", P), ("radius", P), ("fall_velocity", P),
+           ("ec_kind", ctypes.c_int32), ("nf_kind", ctypes.c_int32),
+           ("ec_const", F64), ("eb_const", F64), ("nf_n", F64), ("ec_params", F64 * 13),
+           ("ec_int_mask", I64), ("ec_unit", F64), ("vmin", F64), ("nfmax", F64),
+           ("has_nfmax", ctypes.c_int32), ("handle_all_breakups", ctypes.c_int32),
+           ("max_multiplicity", F64)]
+        + [(n, F64) for n in ("rho_w", "six_over_pi", "pi_sgm_w", "two_thirds", "nf_sc_factor",
+                              "half_rho_w", "micro_joule")]
+        + [("dep_volume", P), ("dep_radius", P), ("dep_velocity", P), ("dep_table_b", P),
+           ("dep_table_c", P), ("dep_radius_scale", F64), ("dep_radius_exponent", F64),
+           ("dep_table_factor", F64), ("dep_radius_max", F64), ("dep_status", P)])
 
 
 KERNELS = {"Golovin": 0, "ConstantK": 1, "Linear": 2, "Geometric": 3, "Hydrodynamic": 4}

@@ -230,7 +230,7 @@ __device__ __forceinline__ HitResult hit_pair(const FusedArgs &a, u32 sj, u32 sk
     if (g != gi) *gamma_slot = gamma;
     r.add_rate = g * n_k;
     r.add_deficit = (gi - g) * n_k;
-    if (gamma != 0.0) {
+    if (gamma != 0.0 && a.skip_coalescence == 0) {
         // coalesce: float arithmetic stored to int64 (quirk A7), attribute update fused (fma)
         const double f_nj = i64_to_f64(n_j), f_nk = i64_to_f64(n_k);
         const double gnk = gamma * f_nk;

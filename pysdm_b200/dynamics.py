@@ -1,4 +1,5 @@
-"""`FusedCoalescence`: PySDM's `Coalescence` dynamic with `step()` mapped onto the one-launch
+"""`FusedCoalescence` / `FusedCollision`: PySDM's `Coalescence` / `Collision` dynamics with
+`step()` mapped onto the one-launch
 fused kernel (csrc/fused*.cu) -- for users of the unchanged PySDM orchestration
 (`Builder`, `Particulator`, attributes, products) who want the collision step at the speed
 `bench.py` measures instead of ~15 backend calls per step:
@@ -18,8 +19,13 @@ the sequence `Collision.step` issues (:196-234) and writes every storage that se
 and for the adaptive time step `dt_left`, `stats_n_substep`, `stats_dt_min`), bit for bit
 (tests/test_gpu_pysdm_backend.py).  The adaptive loop itself (`Collision.__call__`, :174-194:
 sort of `cell_idx` by `dt_left`, `adaptive_sdm_end`, the working-length cut) stays the
-reference's.  Anything else falls through to the reference's `step()` and the method-level
-kernels.
+reference's.  Cells beyond the fused kernel's shared-memory batches (boxes) take the shuffle
+replay + streaming kernel inside the same entry point (csrc/stream.cu).  `FusedCollision`
+(PySDM's `Collision`, i.e. with breakup) runs the step up to compute_gamma the same way and
+the breakup half -- coalescence efficiency (ConstEc / Straub2010Ec / Berry1967), ConstEb,
+fragment mass (AlwaysN / Straub2010Nf), collision_coalescence_breakup -- as one more launch
+(csrc/breakup_fused.cu).  Anything else falls through to the reference's `step()` and the
+method-level kernels.
 """
 
 import warnings
@@ -48,14 +54,26 @@ _KERNELS = {"Golovin": lambda k: (0.0, k.b), "ConstantK": lambda k: (k.a, 0.0),
             "Hydrodynamic": _parameterized}
 
 
-def make_fused_coalescence():
-    """builds the class lazily: importing pysdm_b200 must not need PySDM"""
-    from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+_CLASSES = {}
+
+
+def make_fused_coalescence(which="FusedCoalescence"):
+    """builds the classes lazily: importing pysdm_b200 must not need PySDM"""
+    if not _CLASSES:
+        _CLASSES.update(_make_classes())
+    return _CLASSES[which]
+
+
+def _make_classes():
+    from PySDM.dynamics import Coalescence, Collision  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics.collisions.coalescence_efficiencies._parameterized import (  # pylint: disable=import-outside-toplevel
+        Parameterized as ParameterizedEc)
     from PySDM.dynamics.collisions.collision_kernels.impl.parameterized import Parameterized  # pylint: disable=import-outside-toplevel
+    from PySDM.physics import constants as const  # pylint: disable=import-outside-toplevel
 
     from .backend import B200  # pylint: disable=import-outside-toplevel
 
-    class FusedCoalescence(Coalescence):
+    class FusedStep:  # mixed into the reference's dynamics below
         def __init__(self, *args, **kwargs):
             super().__init__(*args, **kwargs)
             self.n_fused_steps = 0
@@ -144,6 +162,9 @@ def make_fused_coalescence():
             else:
                 attrs.reset_cell_idx()
             self.rnd_opt_coll.reset()
+            if self.enable_breakup:
+                self.rnd_opt_proc.reset()
+                self.rnd_opt_frag.reset()
 
         def _kernel_name(self):
             """name of the fused kernel's instantiation for this configuration, or None when the
@@ -152,13 +173,40 @@ def make_fused_coalescence():
             name = type(self.collision_kernel).__name__
             if isinstance(self.collision_kernel, Parameterized):
                 name = "Hydrodynamic"  # (also `Electric`: Berry's form with other parameters)
-            if (not isinstance(part.backend, B200) or self.enable_breakup
+            if self.enable_breakup and self._breakup_plan() is None:
+                return None
+            if (not isinstance(part.backend, B200)
                     or self.croupier != "local" or name not in _KERNELS
                     or part.n_sd >= 2 ** 32
                     or getattr(part.backend.formulae.particle_shape_and_density, "__name__",
                                "LiquidSpheres") != "LiquidSpheres"):
                 return None
             return name
+
+        def _breakup_plan(self):
+            """keyword arguments of methods.fused_breakup for this dynamic's efficiencies and
+            fragmentation function, or None when the fused breakup kernel does not cover them"""
+            ec, eb, nf = (self.compute_coalescence_efficiency, self.compute_breakup_efficiency,
+                          self.compute_number_of_fragments)
+            plan = {}
+            if type(eb).__name__ != "ConstEb":
+                return None
+            plan["eb_const"] = eb.Eb
+            if type(ec).__name__ == "ConstEc":
+                plan.update(ec_kind=0, ec_const=ec.Ec)
+            elif type(ec).__name__ == "Straub2010Ec":
+                plan.update(ec_kind=1)
+            elif isinstance(ec, ParameterizedEc):  # Berry1967
+                plan.update(ec_kind=2, ec_params=ec.params, ec_unit=const.si.um)
+            else:
+                return None
+            if type(nf).__name__ == "AlwaysN":
+                plan.update(nf_kind=0, nf_n=nf.N)
+            elif type(nf).__name__ == "Straub2010Nf":
+                plan.update(nf_kind=1, vmin=nf.vmin, nfmax=nf.nfmax)
+            else:
+                return None
+            return plan
 
         def _fused_plan(self):
             """(kernel name, a, b, caretaker of the current sort) or None"""
@@ -171,6 +219,45 @@ def make_fused_coalescence():
             if facts is None or part.n_sd >= 2 ** 31:
                 return None
             return (name, *_KERNELS[name](self.collision_kernel), facts)
+
+        def _fused_breakup(self, idx, healthy, ext, length, mass_row, dependents):
+            """collision.py:206-234 after compute_gamma, in one launch"""
+            part, attrs = self.particulator, self.particulator.attributes
+            plan = self._breakup_plan()
+            kw = {}
+            proc, frag = self.rnd_opt_proc, self.rnd_opt_frag
+            if (isinstance(proc.rnd, Random) and not proc.optimized_random
+                    and proc.rnd.seed == frag.rnd.seed):
+                # device Philox: the two uniforms are generated inside the kernel
+                kw.update(seed=proc.rnd.seed, call_proc=proc.rnd.call, call_frag=frag.rnd.call)
+                for opt in (proc, frag):
+                    opt.rnd.call += 1
+                    opt.substep += 1
+            else:
+                kw.update(rand_proc=proc.get_random_arrays().data,
+                          rand_frag=frag.get_random_arrays().data)
+            if plan["ec_kind"] == 1 or plan["nf_kind"] == 1:
+                kw.update(volume=attrs["volume"].data,
+                          fall_velocity=attrs["relative fall velocity"].data)
+            if plan["ec_kind"] == 2 or plan["nf_kind"] == 1:
+                kw["radius"] = attrs["radius"].data
+            constants = part.backend.formulae.constants
+            n_overflow = m.fused_breakup(
+                multiplicity=attrs["multiplicity"].data, idx=idx.data, attributes=ext.data,
+                gamma=self.gamma.data, is_first_in_pair=self.is_first_in_pair.indicator.data,
+                cell_id_=attrs["cell id"].data, healthy=healthy.data,
+                coalescence_rate=self.coalescence_rate.data, breakup_rate=self.breakup_rate.data,
+                breakup_rate_deficit=self.breakup_rate_deficit.data, length=length,
+                mass_row=mass_row, max_multiplicity=self.max_multiplicity,
+                handle_all_breakups=bool(part.backend.formulae.handle_all_breakups),
+                constants={"rho_w": constants.rho_w, "PI": constants.PI,
+                           "sgm_w": constants.sgm_w, "uJ": const.si.uJ},
+                dependents=dependents, count_overflows=bool(self.warn_overflows), **plan, **kw)
+            if self.warn_overflows and n_overflow:
+                import sys  # pylint: disable=import-outside-toplevel
+
+                print(f"overflow ({n_overflow} pairs)\n\tfile: {__file__}"
+                      "\n\tcontext:  collision_coalescence_breakup", file=sys.stderr)
 
         def step(self, want_end=False):  # pylint: disable=arguments-differ
             """one (sub-)step.  `want_end` (adaptive loop): returns adaptive_sdm_end's result
@@ -245,7 +332,8 @@ def make_fused_coalescence():
                 max_cell=facts.max_cell, kernel=name,
                 kernel_a=kernel_a, kernel_b=kernel_b, timestep=part.dt, dv=part.mesh.dv,
                 rho_w=part.backend.rho_w, substeps=substeps, mass_row=mass_row,
-                nf_slot=self._nf_slot, refresh_nf=self._nf_facts != sort_id, **kw)
+                nf_slot=self._nf_slot, refresh_nf=self._nf_facts != sort_id,
+                skip_coalescence=self.enable_breakup, **kw)
             m.check(err, "fused_collision_step")
             self._nf_facts = sort_id
             self._last_facts = facts
@@ -254,6 +342,8 @@ def make_fused_coalescence():
             idx.data, facts.tmp_idx.data = facts.tmp_idx.data, idx.data
             self.is_first_in_pair.length = length
             self.n_fused_steps += 1
+            if self.enable_breakup:
+                self._fused_breakup(idx, healthy, ext, length, mass_row, kw.get("dependents"))
             # Particulator.collision_coalescence_breakup, PySDM/particulator.py:210-213
             end = None
             if want_end:  # `healthy` and the next working length in one read-back
@@ -279,4 +369,10 @@ def make_fused_coalescence():
                     attribute.timestamp = sum(d.timestamp for d in attribute.dependencies)
             return end
 
-    return FusedCoalescence
+    class FusedCoalescence(FusedStep, Coalescence):
+        pass
+
+    class FusedCollision(FusedStep, Collision):
+        pass
+
+    return {"FusedCoalescence": FusedCoalescence, "FusedCollision": FusedCollision}

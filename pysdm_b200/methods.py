@@ -266,7 +266,7 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
                          substeps=1, mass_row=0, u01=None, rand=None, seed=0, call_u01=0,
                          call_rand=0, nf_slot, refresh_nf=True, gate=None, epoch=1, radius=None,
                          fall_velocity=None, berry_params=None, berry_unit=1.0, adaptive=None,
-                         dependents=None, sorted_length=0):
+                         dependents=None, sorted_length=0, skip_coalescence=False):
     """one Collision.step() in one launch; returns the CUDA error code (9 = a cell is
     larger than the fused path supports -> use the method-level functions).  kernel
     "Geometric": kernel_a = PI * collection_efficiency, `radius` and `fall_velocity` = the
@@ -296,6 +296,7 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         ws = WS.dev("fused_stream", nbytes, idx_in.device)
         args.ws, args.ws_bytes = _p(ws), ws.numel()
     args.sorted_length = int(sorted_length)
+    args.skip_coalescence = int(bool(skip_coalescence))
     if adaptive is not None:
         args.adaptive = 1
         args.dt_left = _pf(adaptive["dt_left"])
@@ -323,6 +324,58 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         args.berry_int_mask = int_mask_of(berry_params)
         args.berry_unit = float(berry_unit)
     return _lib.load().pysdm_b200_fused_collision_step(ctypes.byref(args), _stream())
+
+
+def fused_breakup(*, multiplicity, idx, attributes, gamma, is_first_in_pair, cell_id_, healthy,
+                  coalescence_rate, breakup_rate, breakup_rate_deficit, length, mass_row,
+                  ec_kind, nf_kind, ec_const=0.0, eb_const=1.0, nf_n=1.0, ec_params=None,
+                  ec_unit=1.0, vmin=0.0, nfmax=None, handle_all_breakups=False, max_multiplicity,
+                  constants, rand_proc=None, rand_frag=None, seed=0, call_proc=0, call_frag=0,
+                  volume=None, radius=None, fall_velocity=None, dependents=None,
+                  count_overflows=False):
+    """the breakup half of a step in one launch (pysdm_b200_fused_breakup); `constants`: dict with
+    rho_w, PI, sgm_w, uJ as the Formulae / `si` carry them.  Returns the number of overflowing
+    pairs when `count_overflows` (synchronises), else None"""
+    n_attr, n_sd = attributes.shape
+    counter = None
+    if count_overflows:
+        counter = torch.zeros(1, dtype=torch.int64, device=multiplicity.device)
+    pi, rho_w, sgm_w = constants["PI"], constants["rho_w"], constants["sgm_w"]
+    args = _lib.BreakupArgs(
+        multiplicity=_pi(multiplicity), idx=_pi(idx), attributes=_pf(attributes), gamma=_pf(gamma),
+        is_first_in_pair=_pb(is_first_in_pair), cell_id=_pi(cell_id_), healthy=_pi(healthy),
+        coalescence_rate=_pi(coalescence_rate), breakup_rate=_pi(breakup_rate),
+        breakup_rate_deficit=_pi(breakup_rate_deficit), n_overflow=_pi(counter),
+        length=int(length), n_sd=n_sd, n_attr=n_attr, mass_row=int(mass_row),
+        rand_proc=_pf(rand_proc), rand_frag=_pf(rand_frag),
+        seed=int(seed) & 0xFFFFFFFFFFFFFFFF, call_proc=int(call_proc), call_frag=int(call_frag),
+        volume=_pf(volume), radius=_pf(radius), fall_velocity=_pf(fall_velocity),
+        ec_kind=int(ec_kind), nf_kind=int(nf_kind), ec_const=float(ec_const),
+        eb_const=float(eb_const), nf_n=float(nf_n), ec_unit=float(ec_unit), vmin=float(vmin),
+        nfmax=float(0.0 if nfmax is None else nfmax), has_nfmax=int(nfmax is not None),
+        handle_all_breakups=int(bool(handle_all_breakups)),
+        max_multiplicity=float(max_multiplicity),
+        # products formed exactly as the reference's Python forms them
+        rho_w=float(rho_w), six_over_pi=6 / pi, pi_sgm_w=pi * sgm_w, two_thirds=2 / 3,
+        nf_sc_factor=pi * sgm_w * (6 / pi) ** (2 / 3), half_rho_w=rho_w / 2,
+        micro_joule=float(constants["uJ"]))
+    if ec_params is not None:
+        assert len(ec_params) == 13
+        args.ec_params = (ctypes.c_double * 13)(*[float(v) for v in ec_params])
+        args.ec_int_mask = int_mask_of(ec_params)
+    if dependents is not None:
+        args.dep_volume = _pf(dependents.get("volume"))
+        args.dep_radius = _pf(dependents["radius"])
+        args.dep_velocity = _pf(dependents.get("velocity"))
+        args.dep_table_b = _pf(dependents.get("table_b"))
+        args.dep_table_c = _pf(dependents.get("table_c"))
+        args.dep_radius_scale = float(dependents["radius_scale"])
+        args.dep_radius_exponent = float(dependents["radius_exponent"])
+        args.dep_table_factor = float(dependents.get("table_factor", 0.0))
+        args.dep_radius_max = float(dependents.get("radius_max", float("inf")))
+        args.dep_status = _pi(dependents.get("status"))
+    check(_lib.load().pysdm_b200_fused_breakup(ctypes.byref(args), _stream()), "fused_breakup")
+    return int(counter.item()) if count_overflows else None
 
 
 def dependent_attributes(mass, rho_w, *, radius_scale, radius_exponent, table_factor=0.0,

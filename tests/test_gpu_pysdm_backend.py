@@ -207,9 +207,11 @@ def build_physics(pysdm, backend, *, n_sd, dv, dt, attributes, dynamic):
     return builder.build(attributes={k: np.array(v) for k, v in attributes.items()}, products=())
 
 
-def _dynamics(name):
+def _dynamics(name, fused=False):
     # pylint: disable=import-outside-toplevel
     from PySDM.dynamics import Coalescence, Collision
+    if fused:
+        from pysdm_b200 import FusedCoalescence as Coalescence, FusedCollision as Collision
     from PySDM.dynamics.collisions.breakup_efficiencies import ConstEb
     from PySDM.dynamics.collisions.breakup_fragmentations import (AlwaysN, Exponential,
                                                                   Feingold1988, Gaussian,
@@ -279,8 +281,12 @@ PHYSICS_CASES = ("hydrodynamic_adaptive", "geometric", "breakup_straub", "breaku
                  "breakup_feingold", "breakup_slams")
 
 
+FUSED_BREAKUP = ("breakup_straub", "breakup_berry_straub", "breakup_always_n")
+
+
+@pytest.mark.parametrize("fused", (False, True))
 @pytest.mark.parametrize("case", PHYSICS_CASES)
-def test_b200_backend_physics_cases(pysdm, case):
+def test_b200_backend_physics_cases(pysdm, case, fused):
     """Same protocol as above for the gravitational kernels / breakup.  The collision
     probability now goes through pow/exp/log of CUDA's libm, which is not bit-identical to
     glibc's: multiplicities, pair flags, permutation, gamma and the rate counters must still
@@ -303,9 +309,13 @@ def test_b200_backend_physics_cases(pysdm, case):
     if case in FRAG_FUNCTION:
         fkw["fragmentation_function"] = FRAG_FUNCTION[case]
     dv, dt = (1.0, 1.0) if case.startswith("breakup") else (0.05, 10.0)
-    common = dict(n_sd=n_sd, dv=dv, dt=dt, attributes=attributes, dynamic=_dynamics(case))
-    ref = build_physics(pysdm, CPU(Formulae(**fkw)), **common)
-    sut = build_physics(pysdm, B200(Formulae(**fkw), host_rng=True), **common)
+    common = dict(n_sd=n_sd, dv=dv, dt=dt, attributes=attributes)
+    ref = build_physics(pysdm, CPU(Formulae(**fkw)), dynamic=_dynamics(case), **common)
+    # fused=True: pysdm_b200.FusedCoalescence / FusedCollision -- the step (and, for the
+    # efficiencies / fragmentation functions the fused breakup kernel covers, its breakup half)
+    # in one launch each; anything else must fall through to the reference's step()
+    sut = build_physics(pysdm, B200(Formulae(**fkw), host_rng=True),
+                        dynamic=_dynamics(case, fused), **common)
     events = 0
     for step in range(6):
         ref.run(1)
@@ -331,6 +341,12 @@ def test_b200_backend_physics_cases(pysdm, case):
             events += int(dyn_b.breakup_rate.to_ndarray().sum())
         events += int(b["coalescence_rate"].sum())
     assert events > 0
+    if fused:
+        n_fused = sut.dynamics["Collision"].n_fused_steps
+        if case in FUSED_BREAKUP or not case.startswith("breakup"):
+            assert n_fused >= 6, f"{case}: the fused step was expected to run"
+        else:
+            assert n_fused == 0, f"{case}: not covered by the fused breakup kernel"
 
 
 # ---- the dynamics next to the collision step that touch the same SoA state --
@@ -674,11 +690,14 @@ def test_config2_full_size(pysdm):
     attributes = {"volume": volume,
                   "multiplicity": np.full(n_sd, int(239e6 * 10 / n_sd), dtype=np.int64)}
     fkw = dict(fastmath=False, seed=67)
-    common = dict(n_sd=n_sd, dv=10.0, dt=10.0, attributes=attributes,
-                  dynamic=_dynamics("hydrodynamic_adaptive"))
-    ref = build_physics(pysdm, CPU(Formulae(**fkw)), **common)
-    sut = build_physics(pysdm, B200(Formulae(**fkw), host_rng=True), **common)
-    _compare_runs(ref, {"b200": sut}, 3)
+    common = dict(n_sd=n_sd, dv=10.0, dt=10.0, attributes=attributes)
+    ref = build_physics(pysdm, CPU(Formulae(**fkw)), dynamic=_dynamics("hydrodynamic_adaptive"),
+                        **common)
+    suts = {"stock": build_physics(pysdm, B200(Formulae(**fkw), host_rng=True),
+                                   dynamic=_dynamics("hydrodynamic_adaptive"), **common),
+            "fused": build_physics(pysdm, B200(Formulae(**fkw), host_rng=True),
+                                   dynamic=_dynamics("hydrodynamic_adaptive", fused=True), **common)}
+    _compare_runs(ref, suts, 3, fused_expected=("fused",))
 
 
 def test_config3_full_size(pysdm):
@@ -697,8 +716,10 @@ def test_config3_full_size(pysdm):
     attributes = {"volume": volume,
                   "multiplicity": np.full(n_sd, max(1, int(1e3 * 1e6 / n_sd)), dtype=np.int64)}
     fkw = dict(fastmath=False, seed=23, fragmentation_function="Straub2010Nf")
-    common = dict(n_sd=n_sd, dv=1e6, dt=1.0, attributes=attributes,
-                  dynamic=_dynamics("breakup_straub"))
-    ref = build_physics(pysdm, CPU(Formulae(**fkw)), **common)
-    sut = build_physics(pysdm, B200(Formulae(**fkw), host_rng=True), **common)
-    _compare_runs(ref, {"b200": sut}, 2, breakup=True)
+    common = dict(n_sd=n_sd, dv=1e6, dt=1.0, attributes=attributes)
+    ref = build_physics(pysdm, CPU(Formulae(**fkw)), dynamic=_dynamics("breakup_straub"), **common)
+    suts = {"stock": build_physics(pysdm, B200(Formulae(**fkw), host_rng=True),
+                                   dynamic=_dynamics("breakup_straub"), **common),
+            "fused": build_physics(pysdm, B200(Formulae(**fkw), host_rng=True),
+                                   dynamic=_dynamics("breakup_straub", fused=True), **common)}
+    _compare_runs(ref, suts, 2, breakup=True, fused_expected=("fused",))

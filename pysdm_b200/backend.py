@@ -21,7 +21,8 @@ import torch
 
 from . import _lib
 from . import methods as m
-from .random import HostReplayRandom, Random
+from .random import DeferredRandom, HostReplayRandom, Random
+from .recorder import RECORDER, tensors_of
 from .storage import Storage
 
 try:  # drop-in: derive from the reference's own base class when PySDM is importable
@@ -46,7 +47,8 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
     HostReplayRandom = HostReplayRandom
     default_croupier = "local"
 
-    def __init__(self, formulae=None, double_precision=True, device="cuda", host_rng=False):
+    def __init__(self, formulae=None, double_precision=True, device="cuda", host_rng=False,
+                 defer=True):
         if not double_precision:
             raise NotImplementedError("B200 backend is fp64/int64 only")
         _lib.load()  # raises if libpysdm_b200.so has not been built
@@ -68,7 +70,43 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
         # identity_index, not sorted since): lets a caretaker tell a sort under the identity
         # cell order, after which a repeated sort of the untouched idx is a no-op
         self._identity_ptrs = set()
+        # defer=True: the backend calls of a `Collision.step()` are recorded and executed as one
+        # fused launch when they form a step the fused kernel covers (pysdm_b200/recorder.py);
+        # defer=False: every call runs its method-level kernel(s) at once
+        self.defer = bool(defer)
+        if self.defer and not host_rng:
+            self.Random = DeferredRandom
+        self._volume_of = {}  # data pointer of a "volume" tensor -> the mass tensor it came from
+        self._versions = {}   # data pointer of an index tensor -> number of rewrites seen
         BackendMethods.__init__(self)
+
+    # ---- recording (pysdm_b200/recorder.py) ---------------------------------------------------
+    def _record(self, name, run, args, *holders, writes=(), start=False):
+        """records the call when a step is being recorded (or `start`s one); else runs it.
+        `holders`: every storage involved, `writes`: those it writes"""
+        if self.defer and RECORDER.enabled and (start or RECORDER.queue):
+            tensors, written = [], []
+            for h in holders:
+                tensors_of(h, tensors)
+            for h in writes:
+                tensors_of(h, written, with_idx=False)
+            args["backend"] = self
+            if RECORDER.defer(name, run, args, tensors, written):
+                return
+        if RECORDER.queue or RECORDER.lazy:
+            tensors = []
+            for h in holders:
+                tensors_of(h, tensors)
+            RECORDER.sync(tensors)
+        run()
+
+    def volume_source(self, volume):
+        """the mass tensor `volume` was last computed from by volume_of_water_mass, or None"""
+        entry = self._volume_of.get(volume.data_ptr())
+        return entry() if entry is not None else None
+
+    def version_of(self, tensor):
+        return self._versions.get(tensor.data_ptr(), 0)
 
     @property
     def rho_w(self):
@@ -78,6 +116,7 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
     def identity_index(self, idx):  # :13-20
         m.identity_index(idx)
         self._identity_ptrs.add(idx.data_ptr())
+        self._versions[idx.data_ptr()] = self._versions.get(idx.data_ptr(), 0) + 1
 
     @staticmethod
     def shuffle_global(idx, length, u01):  # :22-30
@@ -96,15 +135,20 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
         # what the last sort by cell learnt about `cell_start`: the working length and the largest
         # cell, so that no device sync is needed and populations of small cells take the
         # one-launch shuffle
-        facts = self.sort_facts(cell_start)
-        if facts is None:
-            m.shuffle_local(idx, u01, cell_start, None, None)
-        else:
-            m.shuffle_local(idx, u01, cell_start, facts.length, facts.max_cell)
+        def run():
+            facts = self.sort_facts(cell_start)
+            if facts is None:
+                m.shuffle_local(idx, u01, cell_start, None, None)
+            else:
+                m.shuffle_local(idx, u01, cell_start, facts.length, facts.max_cell)
+
+        self._record("shuffle_local", run, {"idx": idx, "u01": u01, "cell_start": cell_start},
+                     idx, u01, cell_start, writes=(idx,), start=True)
 
     def sort_by_key(self, idx, attr):  # :46-48
         m.sort_by_key(idx.data, attr.data)
         self._identity_ptrs.discard(idx.data.data_ptr())
+        self._versions[idx.data.data_ptr()] = self._versions.get(idx.data.data_ptr(), 0) + 1
 
     @staticmethod
     def remove_zero_n_or_flagged(multiplicity, idx, length):  # collisions_methods.py:664-680
@@ -131,6 +175,9 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
                                                  device=self.tmp_idx.data.device)
 
             def __call__(self, cell_id, cell_idx, cell_start, idx):
+                if RECORDER.queue or RECORDER.lazy:
+                    RECORDER.sync([cell_id.data, cell_idx.data, cell_start.data, idx.data,
+                                   self.tmp_idx.data])
                 m.counting_sort_by_cell_id(self.tmp_idx.data, idx.data, cell_id.data,
                                            cell_idx.data, len(idx), cell_start.data)
                 idx.data, self.tmp_idx.data = self.tmp_idx.data, idx.data
@@ -148,19 +195,33 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
         return CellCaretaker()
 
     # ---- pair methods (pair_methods.py) ---------------------------------------------------
-    @staticmethod
-    def find_pairs(cell_start, is_first_in_pair, cell_id, cell_idx, idx):  # :34-55
-        m.find_pairs(cell_start.data, is_first_in_pair.indicator.data, cell_id.data,
-                     cell_idx.data, idx.data, len(idx))
+    def find_pairs(self, cell_start, is_first_in_pair, cell_id, cell_idx, idx):  # :34-55
+        def run():
+            m.find_pairs(cell_start.data, is_first_in_pair.indicator.data, cell_id.data,
+                         cell_idx.data, idx.data, len(idx))
 
-    @staticmethod
-    def sort_within_pair_by_attr(idx, is_first_in_pair, attr):  # :126-140
-        m.sort_within_pair_by_attr(idx.data, len(idx), is_first_in_pair.indicator.data, attr.data)
+        self._record("find_pairs", run, {"cell_start": cell_start, "flags": is_first_in_pair,
+                                         "cell_id": cell_id, "cell_idx": cell_idx, "idx": idx},
+                     cell_start, is_first_in_pair, cell_id, cell_idx, idx,
+                     writes=(is_first_in_pair,))
 
-    @staticmethod
-    def _pair(op, data_out, data_in, is_first_in_pair, idx):
-        m.pair_op(op, data_out.data, data_in.data, is_first_in_pair.indicator.data, idx.data,
-                  len(idx))
+    def sort_within_pair_by_attr(self, idx, is_first_in_pair, attr):  # :126-140
+        def run():
+            m.sort_within_pair_by_attr(idx.data, len(idx), is_first_in_pair.indicator.data,
+                                       attr.data)
+
+        self._record("sort_within_pair_by_attr", run,
+                     {"idx": idx, "flags": is_first_in_pair, "attr": attr},
+                     idx, is_first_in_pair, attr, writes=(idx,))
+
+    def _pair(self, op, data_out, data_in, is_first_in_pair, idx):
+        def run():
+            m.pair_op(op, data_out.data, data_in.data, is_first_in_pair.indicator.data, idx.data,
+                      len(idx))
+
+        self._record("pair_op", run, {"op": op, "out": data_out, "in": data_in,
+                                      "flags": is_first_in_pair, "idx": idx},
+                     data_out, data_in, is_first_in_pair, idx, writes=(data_out,))
 
     def distance_pair(self, data_out, data_in, is_first_in_pair, idx):  # :14-32
         self._pair("distance", data_out, data_in, is_first_in_pair, idx)
@@ -183,10 +244,16 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
                     len(idx))
 
     # ---- collision methods (collisions_methods.py) -----------------------------------------
-    @staticmethod
-    def normalize(prob, cell_id, cell_idx, cell_start, norm_factor, timestep, dv):  # :633-662
-        m.normalize(prob.data, cell_id.data, cell_idx.data, cell_start.data, norm_factor.data,
-                    timestep, dv)
+    def normalize(self, prob, cell_id, cell_idx, cell_start, norm_factor, timestep, dv):  # :633-662
+        def run():
+            m.normalize(prob.data, cell_id.data, cell_idx.data, cell_start.data,
+                        norm_factor.data, timestep, dv)
+
+        self._record("normalize", run, {"prob": prob, "cell_id": cell_id, "cell_idx": cell_idx,
+                                        "cell_start": cell_start, "norm_factor": norm_factor,
+                                        "timestep": timestep, "dv": dv},
+                     prob, cell_id, cell_idx, cell_start, norm_factor,
+                     writes=(prob, norm_factor))
 
     @staticmethod
     def adaptive_sdm_end(dt_left, cell_start):  # :313-328
@@ -201,19 +268,35 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
             dt_left.data, dt, dt_range, is_first_in_pair.indicator.data, stats_n_substep.data,
             stats_dt_min.data)
 
-    @staticmethod
-    def compute_gamma(*, prob, rand, multiplicity, cell_id, collision_rate_deficit,
+    def compute_gamma(self, *, prob, rand, multiplicity, cell_id, collision_rate_deficit,
                       collision_rate, is_first_in_pair, out):  # :522-585
-        m.compute_gamma(prob.data, rand.data, multiplicity.idx.data, len(multiplicity),
-                        multiplicity.data, cell_id.data, collision_rate_deficit.data,
-                        collision_rate.data, is_first_in_pair.indicator.data, out.data)
+        def run():
+            m.compute_gamma(prob.data, rand.data, multiplicity.idx.data, len(multiplicity),
+                            multiplicity.data, cell_id.data, collision_rate_deficit.data,
+                            collision_rate.data, is_first_in_pair.indicator.data, out.data)
 
-    @staticmethod
-    def collision_coalescence(*, multiplicity, idx, attributes, gamma, healthy, cell_id,
+        self._record("compute_gamma", run,
+                     {"prob": prob, "rand": rand, "multiplicity": multiplicity, "cell_id": cell_id,
+                      "collision_rate_deficit": collision_rate_deficit,
+                      "collision_rate": collision_rate, "flags": is_first_in_pair, "out": out},
+                     prob, rand, multiplicity, cell_id, collision_rate_deficit, collision_rate,
+                     is_first_in_pair, out,
+                     writes=(out, collision_rate_deficit, collision_rate))
+
+    def collision_coalescence(self, *, multiplicity, idx, attributes, gamma, healthy, cell_id,
                               coalescence_rate, is_first_in_pair):  # :418-477
-        m.collision_coalescence(multiplicity.data, idx.data, len(idx), attributes.data,
-                                gamma.data, healthy.data, cell_id.data, coalescence_rate.data,
-                                is_first_in_pair.indicator.data)
+        def run():
+            m.collision_coalescence(multiplicity.data, idx.data, len(idx), attributes.data,
+                                    gamma.data, healthy.data, cell_id.data,
+                                    coalescence_rate.data, is_first_in_pair.indicator.data)
+
+        self._record("collision_coalescence", run,
+                     {"multiplicity": multiplicity, "idx": idx, "attributes": attributes,
+                      "gamma": gamma, "healthy": healthy, "cell_id": cell_id,
+                      "coalescence_rate": coalescence_rate, "flags": is_first_in_pair},
+                     multiplicity, idx, attributes, gamma, healthy, cell_id, coalescence_rate,
+                     is_first_in_pair,
+                     writes=(multiplicity, attributes, healthy, coalescence_rate))
 
     def collision_coalescence_breakup(self, *, multiplicity, idx, attributes, gamma, rand, Ec,
                                       Eb, fragment_mass, healthy, cell_id, coalescence_rate,
@@ -237,9 +320,14 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
 
     def linear_collection_efficiency(self, *, params, output, radii, is_first_in_pair, unit):
         # :743-782
-        m.linear_collection_efficiency(params, m.int_mask_of(params), output.data, radii.data,
-                                       is_first_in_pair.indicator.data, radii.idx.data,
-                                       len(is_first_in_pair), unit)
+        def run():
+            m.linear_collection_efficiency(params, m.int_mask_of(params), output.data, radii.data,
+                                           is_first_in_pair.indicator.data, radii.idx.data,
+                                           len(is_first_in_pair), unit)
+
+        self._record("lce", run, {"params": params, "output": output, "radii": radii,
+                                  "flags": is_first_in_pair, "unit": unit},
+                     output, radii, is_first_in_pair, writes=(output,))
 
     # ---- terminal velocities (terminal_velocity_methods.py) ---------------------------------
     @staticmethod
@@ -364,12 +452,69 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
                   number_of_super_particles_to_inject)
 
     # ---- physics (physics_methods.py:107-133) -----------------------------------------------
+    def _liquid_spheres_only(self):
+        """the reference dispatches these through formulae.particle_shape_and_density
+        (physics_methods.py:107-133); only LiquidSpheres (m = rho_w v) is implemented here --
+        MixedPhaseSpheres (rho_i for negative, i.e. ice, masses) must not silently get it"""
+        name = getattr(self.formulae.particle_shape_and_density, "__name__", "LiquidSpheres")
+        if name != "LiquidSpheres":
+            raise NotImplementedError(f"B200 backend: particle_shape_and_density={name}")
+
     def volume_of_water_mass(self, volume, mass):
+        self._liquid_spheres_only()
         m.volume_of_water_mass(volume.data, mass.data, self.rho_w)
+        self._volume_of[volume.data.data_ptr()] = weakref.ref(mass.data)
 
     def mass_of_water_volume(self, mass, volume):
+        self._liquid_spheres_only()
         m.mass_of_water_volume(mass.data, volume.data, self.rho_w)
 
+
+# every method that is not recorded itself first lets the recorder replay what it has, if the
+# call touches memory the record reads or writes (pysdm_b200/recorder.py)
+_RECORDED = {"shuffle_local", "find_pairs", "sort_within_pair_by_attr", "_pair", "distance_pair",
+             "max_pair", "min_pair", "sum_pair", "multiply_pair", "normalize", "compute_gamma",
+             "collision_coalescence", "linear_collection_efficiency", "_record", "volume_source",
+             "version_of", "sort_facts", "rho_w", "_liquid_spheres_only",
+             "_need_fragmentation_function"}
+
+
+_READ_ONLY = {"volume_of_water_mass": ("mass",), "mass_of_water_volume": ("volume",),
+              "interpolation": ("radius", "b", "c"), "terminal_velocity": ("radius",),
+              "power_series": ("radius",)}
+
+
+def _guarded(function):
+    import functools  # pylint: disable=import-outside-toplevel
+
+    # (only this method reads the permutation through `multiplicity.idx`)
+    with_idx = function.__name__ == "scale_prob_for_adaptive_sdm_gamma"
+    # the recalculations of derived attributes the orchestration triggers in the middle of a
+    # step only READ these arguments (everything else counts as written)
+    read_only = _READ_ONLY.get(function.__name__, ())
+    names = function.__code__.co_varnames[:function.__code__.co_argcount
+                                          + function.__code__.co_kwonlyargcount]
+
+    @functools.wraps(function)
+    def wrapper(*args, **kwargs):
+        if RECORDER.queue or RECORDER.lazy:
+            writes, reads = [], []
+            for name, a in list(zip(names, args)) + list(kwargs.items()):
+                tensors_of(a, reads if name in read_only else writes, with_idx)
+            RECORDER.sync(writes, reads)
+        return function(*args, **kwargs)
+
+    return wrapper
+
+
+for _name, _member in list(vars(B200).items()):
+    if _name.startswith("__") or _name in _RECORDED or isinstance(_member, property):
+        continue
+    if isinstance(_member, staticmethod):
+        setattr(B200, _name, staticmethod(_guarded(_member.__func__)))
+    elif callable(_member) and not isinstance(_member, type):
+        setattr(B200, _name, _guarded(_member))
+del _name, _member
 
 # everything outside the collision path (SURVEY.md 8b): explicit NotImplementedError
 for _name in (

@@ -163,7 +163,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.collision_rate = full(self.n_cell, 0, i64)
         self.collision_rate_deficit = full(self.n_cell, 0, i64)
         self.coalescence_rate = full(self.n_cell, 0, i64)
-        self.status = full(1, 0, i64)
+        self.status = self._words[3:4]  # fused step: a batch of cells did not fit (wrong hint)
         self.nf_slot = full(n_pairs, nan, f64)  # fused step: normalize factor per pair slot
         self.nf_valid = False  # False after anything that changes cell_start/cell_idx/cell_id
         # RandomGeneratorOptimizer.register
@@ -253,9 +253,16 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         return self.cell_start
 
     def is_healthy(self):
-        self._healthy_host.copy_(self.healthy, non_blocking=True)
+        self._words_host.copy_(self._words, non_blocking=True)
         torch.cuda.current_stream().synchronize()
-        return bool(self._healthy_host[0])
+        self._check_status(self._words_host)
+        return bool(self._words_host[0])
+
+    @staticmethod
+    def _check_status(words):
+        if words[3]:
+            raise RuntimeError("fused collision step: a batch of cells exceeded the size the "
+                               "last sort by cell reported")
 
     def sanitize(self):
         if not self.is_healthy():
@@ -311,6 +318,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
                     self.step_fused()
                     self._words_host.copy_(self._words, non_blocking=True)
                     torch.cuda.current_stream().synchronize()
+                    self._check_status(self._words_host)
                     if self._words_host[0]:
                         end = int(self._words_host[1])
                     else:
@@ -415,6 +423,9 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
 
     def drain(self):
         """waits for the steps in flight and sanitizes after them, as step() would have"""
+        if self._in_flight:  # (the error flag of the speculated launches, once per drain)
+            self._in_flight[-1][0].synchronize()
+            self._check_status(self._words.cpu())
         while self._in_flight:
             if not self._resolved_healthy(self._in_flight.pop(0)):
                 redo = len(self._in_flight)

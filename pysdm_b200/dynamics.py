@@ -34,6 +34,7 @@ import torch
 
 from . import methods as m
 from .random import Random
+from .recorder import RECORDER
 
 
 def _geometric(k):
@@ -86,11 +87,14 @@ def _make_classes():
             dev = self.gamma.data.device
             self._nf_slot = torch.full((self.particulator.n_sd // 2,), float("nan"),
                                        dtype=torch.float64, device=dev)
-            self._status = torch.zeros(1, dtype=torch.int64, device=dev)
             self._rank_info = torch.zeros(self.particulator.mesh.n_cell, dtype=torch.int64,
                                           device=dev)
-            self._words = torch.zeros(4, dtype=torch.int64, device=dev)  # [healthy, end, ...]
+            # what the host reads back after a fused (sub-)step, in one copy: [0] `healthy`,
+            # [1] adaptive_sdm_end's result, [2] a derived radius left the Gunn-Kinzer table,
+            # [3] `status` of the fused step (a batch of cells did not fit: wrong size hint)
+            self._words = torch.zeros(4, dtype=torch.int64, device=dev)
             self._words_host = torch.zeros(4, dtype=torch.int64).pin_memory()
+            self._status = self._words[3:4]
             self._dependents = self._dependent_chain(builder)
 
         def _dependent_chain(self, builder):
@@ -116,7 +120,7 @@ def _make_classes():
                 return None
             return {"chain": (mass, volume, radius, velocity), "approximation": approximation,
                     "radius_scale": 1 / formulae.constants.PI_4_3, "radius_exponent": 1 / 3,
-                    "status": torch.zeros(1, dtype=torch.int64, device=self.gamma.data.device)}
+                    "status": self._words[2:3]}
 
         def __call__(self):
             fused_before = self.n_fused_steps
@@ -124,11 +128,6 @@ def _make_classes():
                 self._adaptive_loop()  # (falls back per sub-step when a cell is too large)
             else:
                 super().__call__()
-            if self._dependents is not None and self.n_fused_steps > fused_before:
-                if int(self._dependents["status"].item()):  # gunn_and_kinzer.py:129-133
-                    raise ValueError(
-                        f"Radii can be interpolated up to "
-                        f"{self._dependents['approximation'].maximum_radius} m")
             if self.adaptive and self.n_fused_steps > fused_before:
                 # the reference looks at this after every sub-step (collision.py:276-277); the
                 # fused sub-steps leave it to one look per time step (stats_dt_min only falls)
@@ -242,6 +241,7 @@ def _make_classes():
             if plan["ec_kind"] == 2 or plan["nf_kind"] == 1:
                 kw["radius"] = attrs["radius"].data
             constants = part.backend.formulae.constants
+            RECORDER.flush_all()
             n_overflow = m.fused_breakup(
                 multiplicity=attrs["multiplicity"].data, idx=idx.data, attributes=ext.data,
                 gamma=self.gamma.data, is_first_in_pair=self.is_first_in_pair.indicator.data,
@@ -320,6 +320,7 @@ def _make_classes():
             length = len(idx)
             ext = attrs.get_extensive_attribute_storage()
             sort_id = (facts, facts.n_sorts)
+            RECORDER.flush_all()  # (this class drives the kernels directly: nothing may be pending)
             err = m.fused_collision_step(
                 idx_in=idx.data, idx_out=facts.tmp_idx.data, cell_start=attrs.cell_start.data,
                 cell_idx=attrs.cell_idx.data, cell_id_=attrs["cell id"].data,
@@ -345,17 +346,22 @@ def _make_classes():
             if self.enable_breakup:
                 self._fused_breakup(idx, healthy, ext, length, mass_row, kw.get("dependents"))
             # Particulator.collision_coalescence_breakup, PySDM/particulator.py:210-213
+            # one read-back: `healthy` (what sanitize() would read), the next working length, and
+            # the two error flags of the launch
             end = None
-            if want_end:  # `healthy` and the next working length in one read-back
-                self._words[0:1].copy_(healthy.data)
-                self._words_host.copy_(self._words, non_blocking=True)
-                torch.cuda.current_stream().synchronize()
-                if self._words_host[0]:
-                    end = int(self._words_host[1])  # (sanitize() would find nothing to do)
-                else:
-                    attrs.sanitize()  # removes the dead super-droplets; idx is re-sorted next
-            else:
-                attrs.sanitize()
+            self._words[0:1].copy_(healthy.data)
+            self._words_host.copy_(self._words, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            if self._words_host[3]:
+                raise RuntimeError("fused collision step: a batch of cells exceeded the size the "
+                                   "last sort by cell reported")
+            if self._words_host[2]:  # gunn_and_kinzer.py:129-133
+                raise ValueError("Radii can be interpolated up to "
+                                 f"{self._dependents['approximation'].maximum_radius} m")
+            if not self._words_host[0]:
+                attrs.sanitize()  # removes the dead super-droplets; idx is re-sorted next
+            elif want_end:
+                end = int(self._words_host[1])
             attrs.mark_updated("multiplicity")
             for key in attrs.get_extensive_attribute_keys():
                 attrs.mark_updated(key)

@@ -14,6 +14,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from .recorder import RECORDER
 from .storage import DEVICE, ptr, stream
 
 
@@ -25,11 +26,30 @@ class Random:  # pylint: disable=too-few-public-methods
         self.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
         self.call = 0
 
+    # the fill may be recorded instead of executed (pysdm_b200/recorder.py): when the step it
+    # belongs to runs as a fused launch the kernel generates the same elements itself
+    defer = False
+
     def __call__(self, storage):
-        data = storage.data
-        _lib.check(_lib.load().pysdm_b200_philox_uniform(
-            ptr(data), data.numel(), self.seed, self.call, stream()), "philox_uniform")
+        data, seed, call = storage.data, self.seed, self.call
         self.call += 1
+
+        def run():
+            _lib.check(_lib.load().pysdm_b200_philox_uniform(
+                ptr(data), data.numel(), seed, call, stream()), "philox_uniform")
+
+        if (self.defer and RECORDER.enabled and data.dim() == 1
+                and RECORDER.defer("philox_fill", run, {"tensor": data, "seed": seed,
+                                                        "call": call}, [data])):
+            return
+        if RECORDER.queue or RECORDER.lazy:
+            RECORDER.sync([data])
+        run()
+
+
+class DeferredRandom(Random):  # pylint: disable=too-few-public-methods
+    """`Random` of a B200 backend that records collision steps"""
+    defer = True
 
 
 class HostReplayRandom:  # pylint: disable=too-few-public-methods
@@ -42,4 +62,6 @@ class HostReplayRandom:  # pylint: disable=too-few-public-methods
 
     def __call__(self, storage):
         host = self.generator.uniform(0, 1, storage.shape)
+        if RECORDER.queue or RECORDER.lazy:
+            RECORDER.sync([storage.data])
         storage.data.copy_(torch.from_numpy(host).to(DEVICE, non_blocking=False))

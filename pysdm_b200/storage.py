@@ -12,6 +12,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from .recorder import RECORDER
 
 try:  # when PySDM is importable the reference's own base classes are used (drop-in)
     from PySDM.backends.impl_common.storage_utils import StorageBase, StorageSignature
@@ -162,6 +163,7 @@ class Storage(StorageBase):
             return Storage(StorageSignature(self.data[item], shape, self.dtype))
         if isinstance(item, tuple) and dim == 2 and isinstance(item[1], slice):
             return Storage(StorageSignature(self.data[item[0]], (*self.shape[1:],), self.dtype))
+        self._peek()
         return self.data[item].item()  # host scalar (device sync)
 
     def __setitem__(self, key, value):
@@ -169,15 +171,43 @@ class Storage(StorageBase):
             value = value.data
         elif isinstance(value, np.ndarray):
             value = torch.from_numpy(np.ascontiguousarray(value)).to(DEVICE)
+        self._touch(value)
         self.data[key] = value
         return self
 
     # ---- arithmetic (own kernels) -----------------------------------------------------
+    def _touch(self, *others):
+        """before this storage's memory is written (and `others` read) outside the record of a
+        collision step (pysdm_b200/recorder.py)"""
+        if RECORDER.queue or RECORDER.lazy:
+            RECORDER.sync([self.data], [o for o in others if isinstance(o, torch.Tensor)])
+
+    def _peek(self):
+        """before this storage's memory is read"""
+        if RECORDER.queue or RECORDER.lazy:
+            RECORDER.sync((), [self.data])
+
     def _ew(self, op, a=None, b=None, scalar=0.0, out=None):
         assert self.dtype is Storage.FLOAT, "elementwise arithmetic is defined for fp64 storages"
         out = self.data if out is None else out
-        _lib.check(_lib.load().pysdm_b200_elementwise(
-            _lib.EW[op], ptr(out), ptr(a), ptr(b), float(scalar), out.numel(), stream()), op)
+
+        def run():
+            _lib.check(_lib.load().pysdm_b200_elementwise(
+                _lib.EW[op], ptr(out), ptr(a), ptr(b), float(scalar), out.numel(), stream()), op)
+
+        if RECORDER.queue or RECORDER.lazy:
+            tensors = [t for t in (out, a, b) if t is not None]
+            # in-place `*= += **= /=` on storages a recorded collision step has written are part
+            # of the record (e.g. `output *= b` after sum_pair); unrelated ones (the `**= 1/3` of
+            # the radius attribute, recalculated in the middle of a step) run at once
+            if (RECORDER.queue and RECORDER.enabled and a is out
+                    and op in ("mul", "add", "pow", "div")
+                    and any(t.untyped_storage().data_ptr() in RECORDER.touched for t in tensors)
+                    and RECORDER.defer("ew", run, {"op": op, "out": out, "a": a, "b": b,
+                                                   "scalar": float(scalar)}, tensors, [out])):
+                return self
+            RECORDER.sync([out], [t for t in (a, b) if t is not None and t is not out])
+        run()
         return self
 
     @staticmethod
@@ -195,6 +225,7 @@ class Storage(StorageBase):
             return self._ew("axpy", self.data, other[2].data, other[0])
         if self.dtype is not Storage.FLOAT:
             tensor, scalar = self._operand(other)
+            self._touch(tensor)
             self.data += tensor if tensor is not None else int(scalar)
             return self
         tensor, scalar = self._operand(other)
@@ -203,6 +234,7 @@ class Storage(StorageBase):
     def __isub__(self, other):
         if self.dtype is Storage.FLOAT and getattr(other, "dtype", None) is Storage.INT:
             # position_in_cell -= floor_of_position (dynamics/displacement.py:150)
+            self._touch(other.data)
             _lib.check(_lib.load().pysdm_b200_sub_i64(ptr(self.data), ptr(other.data),
                                                      self.data.numel(), stream()), "sub_int")
             return self
@@ -218,6 +250,7 @@ class Storage(StorageBase):
 
     def __imod__(self, other):
         n_rows, n_cols = (self.shape if len(self.shape) == 2 else (1, self.shape[0]))
+        self._touch(other.data)
         if self.dtype is Storage.INT:  # cell_origin %= grid (dynamics/displacement.py:152-153)
             _lib.check(_lib.load().pysdm_b200_row_modulo_i64(
                 ptr(self.data), ptr(other.data), n_rows, n_cols, stream()), "row_modulo")
@@ -231,6 +264,7 @@ class Storage(StorageBase):
 
     def floor(self, other=None):
         if self.dtype is Storage.INT:  # floor_of_position.floor(position_in_cell), :147-148
+            self._touch(other.data)
             _lib.check(_lib.load().pysdm_b200_floor_to_i64(
                 ptr(self.data), ptr(other.data), self.data.numel(), stream()), "floor")
             return self
@@ -257,6 +291,7 @@ class Storage(StorageBase):
 
     # ---- reductions (host result => device sync) ---------------------------------------
     def _minmax(self, is_max):
+        self._peek()
         lib = _lib.load()
         scratch = SCRATCH.device("reduce", lib.pysdm_b200_reduce_scratch_bytes())
         box = SCRATCH.host()
@@ -282,19 +317,23 @@ class Storage(StorageBase):
         return self._minmax(True)
 
     def all(self):
+        self._peek()
         return bool(torch.all(self.data != 0).item())
 
     def __bool__(self):
         if len(self) == 1:
+            self._peek()
             return bool(self.data[0].item() != 0)
         raise NotImplementedError("Logic value of array is ambiguous.")
 
     # ---- memory plumbing ---------------------------------------------------------------
     def detach(self):
+        self._touch()
         if self.data._base is not None:  # pylint: disable=protected-access
             self.data = self.data.clone()
 
     def download(self, target, reshape=False):
+        self._peek()
         if isinstance(target, torch.Tensor):  # straight into (pinned) host memory
             target.copy_(self.data.reshape(target.shape))
             return
@@ -304,9 +343,11 @@ class Storage(StorageBase):
         np.copyto(target, host, casting="safe")
 
     def to_ndarray(self):
+        self._peek()
         return self.data.cpu().numpy().copy()
 
     def upload(self, data):
+        self._touch()
         if isinstance(data, torch.Tensor):  # (pinned) host tensor of the storage's own dtype
             self.data.copy_(data.reshape(self.data.shape), non_blocking=True)
             return
@@ -316,12 +357,23 @@ class Storage(StorageBase):
     def ravel(self, other):
         src = other.data if isinstance(other, Storage) else torch.from_numpy(
             np.ascontiguousarray(other)).to(DEVICE)
+        self._touch(src)
         self.data[:] = src.reshape(-1)
 
     def urand(self, generator):
         generator(self)
 
     def fill(self, other):
+        if (RECORDER.queue and RECORDER.enabled and self.dtype is Storage.FLOAT
+                and isinstance(other, (int, float)) and not isinstance(other, bool)):
+            out, value = self.data, float(other)  # `output.fill(a)` of a recorded collision step
+
+            def run():
+                out[:] = value
+
+            if RECORDER.defer("fill", run, {"out": out, "scalar": value}, [out]):
+                return
+        self._touch(other.data if isinstance(other, Storage) else None)
         if isinstance(other, Storage):
             self.data[:] = other.data
         elif isinstance(other, np.ndarray):

@@ -118,8 +118,11 @@ def test_b200_backend_equals_numba_backend(pysdm, case):
     seed = 1234
     common = dict(n_sd=n_sd, grid=c["grid"], dv=c["dv"], dt=1.0, attributes=attributes,
                   dynamic_kw=c["kw"])
+    from pysdm_b200.recorder import RECORDER  # pylint: disable=import-outside-toplevel
+
     ref = build(pysdm, CPU(Formulae(fastmath=False, seed=seed)), **common)
     sut = build(pysdm, B200(Formulae(fastmath=False, seed=seed), host_rng=True), **common)
+    fused0, replayed0 = RECORDER.n_fused, RECORDER.n_replayed
     collided = 0
     for step in range(8):
         ref.run(1)
@@ -138,6 +141,14 @@ def test_b200_backend_equals_numba_backend(pysdm, case):
             np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
         collided = int(b["coalescence_rate"].sum())
     assert collided > 0
+    # the stock dynamic's backend calls are recorded and run as one fused launch per step when
+    # they form a step the fused kernel covers (pysdm_b200/recorder.py); the adaptive sequence
+    # (a host read of stats_dt_min in its middle) and the global croupier are replayed / eager
+    if case in ("local", "substeps", "box", "box_stream"):
+        assert RECORDER.n_fused - fused0 == 8 * c["kw"].get("substeps", 1)
+        assert RECORDER.n_replayed == replayed0
+    else:
+        assert RECORDER.n_fused == fused0
 
 
 @pytest.mark.parametrize("host_rng", (True, False))
@@ -723,3 +734,73 @@ def test_config3_full_size(pysdm):
             "fused": build_physics(pysdm, B200(Formulae(**fkw), host_rng=True),
                                    dynamic=_dynamics("breakup_straub", fused=True), **common)}
     _compare_runs(ref, suts, 2, breakup=True, fused_expected=("fused",))
+
+
+@pytest.mark.parametrize("kernel", ("Golovin", "ConstantK", "Geometric", "Hydrodynamic",
+                                    "SimpleGeometric"))
+def test_recorded_stock_dynamic_equals_eager(pysdm, kernel):
+    """`Builder(backend=B200())` with the STOCK `Coalescence`: the recording backend
+    (pysdm_b200/recorder.py: one fused launch per step, uniforms generated in the kernel, the
+    two `Random` fills elided) against the same backend executing every call at once
+    (`B200(defer=False)`), same device Philox stream -- everything bit-identical after every
+    step.  SimpleGeometric is a sequence the fused kernel does not cover: the record must be
+    replayed call by call."""
+    from PySDM import Builder, Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics.collisions.collision_kernels import (  # pylint: disable=import-outside-toplevel
+        ConstantK, Geometric, Golovin, Hydrodynamic, SimpleGeometric)
+    from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
+    from PySDM.impl.mesh import Mesh  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200  # pylint: disable=import-outside-toplevel
+    from pysdm_b200.recorder import RECORDER  # pylint: disable=import-outside-toplevel
+
+    n_sd, grid = 6000, (5, 6)
+    rng = np.random.default_rng(41)
+    attributes = {
+        "multiplicity": rng.integers(1, 40, n_sd).astype(np.int64),
+        "volume": 4 / 3 * np.pi * (rng.exponential(12e-6, n_sd) + 2e-6) ** 3,
+        "cell id": rng.integers(0, 30, n_sd).astype(np.int64),
+    }
+    make_kernel = {"Golovin": lambda: Golovin(b=1.5e3), "ConstantK": lambda: ConstantK(a=3e-11),
+                   "Geometric": lambda: Geometric(collection_efficiency=0.9),
+                   "Hydrodynamic": Hydrodynamic, "SimpleGeometric": lambda: SimpleGeometric(C=3e5)}
+    dv = {"Golovin": 1e-7, "ConstantK": 1e-6}.get(kernel, 2e-5)
+
+    def make(backend):
+        env = Box(dv=dv, dt=10.0)
+        env.mesh = Mesh(grid, size=grid, dv=dv)
+        builder = Builder(n_sd=n_sd, backend=backend, environment=env)
+        builder.add_dynamic(Coalescence(collision_kernel=make_kernel[kernel](), adaptive=False,
+                                        substeps=2))
+        return builder.build(attributes={k: v.copy() for k, v in attributes.items()}, products=())
+
+    fkw = dict(fastmath=False, seed=91)
+    ref = make(B200(Formulae(**fkw), defer=False))
+    sut = make(B200(Formulae(**fkw)))
+    fused0, replayed0 = RECORDER.n_fused, RECORDER.n_replayed
+    for step in range(5):
+        ref.run(1)
+        sut.run(1)
+        a, b = snapshot(sut), snapshot(ref)
+        n = b["length"]
+        assert a["length"] == n, f"step {step}: length"
+        np.testing.assert_array_equal(a["idx"][:n], b["idx"][:n], f"step {step}: idx")
+        np.testing.assert_array_equal(a["flag"][:n], b["flag"][:n], f"step {step}: flag")
+        np.testing.assert_array_equal(a["multiplicity"], b["multiplicity"], f"step {step}")
+        assert_same_f64(a["attributes"], b["attributes"], f"step {step}: attributes")
+        assert_same_f64(a["gamma"], b["gamma"], f"step {step}: gamma")
+        for k in ("collision_rate", "collision_rate_deficit", "coalescence_rate"):
+            np.testing.assert_array_equal(a[k], b[k], f"step {step}: {k}")
+        # the uniform arrays of a fused step were never written; reading them fills them
+        dyn_a, dyn_b = sut.dynamics["Collision"], ref.dynamics["Collision"]
+        if step == 2:
+            assert_same_f64(dyn_a.rnd_opt_coll.pairs_rand.to_ndarray(),
+                            dyn_b.rnd_opt_coll.pairs_rand.to_ndarray(), "pairs_rand")
+            assert_same_f64(dyn_a.rnd_opt_coll.rand.to_ndarray(),
+                            dyn_b.rnd_opt_coll.rand.to_ndarray(), "rand")
+    assert int(snapshot(ref)["coalescence_rate"].sum()) > 0
+    if kernel == "SimpleGeometric":
+        assert RECORDER.n_fused == fused0 and RECORDER.n_replayed > replayed0
+    else:
+        assert RECORDER.n_fused - fused0 == 10 and RECORDER.n_replayed == replayed0

@@ -93,7 +93,7 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
             args["backend"] = self
             if RECORDER.defer(name, run, args, tensors, written):
                 return
-        if RECORDER.queue or RECORDER.lazy:
+        if RECORDER.busy():
             tensors = []
             for h in holders:
                 tensors_of(h, tensors)
@@ -175,7 +175,7 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
                                                  device=self.tmp_idx.data.device)
 
             def __call__(self, cell_id, cell_idx, cell_start, idx):
-                if RECORDER.queue or RECORDER.lazy:
+                if RECORDER.busy():
                     RECORDER.sync([cell_id.data, cell_idx.data, cell_start.data, idx.data,
                                    self.tmp_idx.data])
                 m.counting_sort_by_cell_id(self.tmp_idx.data, idx.data, cell_id.data,
@@ -462,6 +462,11 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
 
     def volume_of_water_mass(self, volume, mass):
         self._liquid_spheres_only()
+        entry = RECORDER.current.get(volume.data.data_ptr())
+        if entry is not None and entry[0] == mass.data.data_ptr():
+            return  # a fused launch kept it current and nothing wrote mass or volume since
+        if RECORDER.busy():
+            RECORDER.sync([volume.data], [mass.data])
         m.volume_of_water_mass(volume.data, mass.data, self.rho_w)
         self._volume_of[volume.data.data_ptr()] = weakref.ref(mass.data)
 
@@ -475,6 +480,7 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
 _RECORDED = {"shuffle_local", "find_pairs", "sort_within_pair_by_attr", "_pair", "distance_pair",
              "max_pair", "min_pair", "sum_pair", "multiply_pair", "normalize", "compute_gamma",
              "collision_coalescence", "linear_collection_efficiency", "_record", "volume_source",
+             "volume_of_water_mass",
              "version_of", "sort_facts", "rho_w", "_liquid_spheres_only",
              "_need_fragmentation_function"}
 
@@ -497,7 +503,7 @@ def _guarded(function):
 
     @functools.wraps(function)
     def wrapper(*args, **kwargs):
-        if RECORDER.queue or RECORDER.lazy:
+        if RECORDER.busy():
             writes, reads = [], []
             for name, a in list(zip(names, args)) + list(kwargs.items()):
                 tensors_of(a, reads if name in read_only else writes, with_idx)

@@ -255,6 +255,12 @@ __device__ __forceinline__ HitResult hit_pair(const FusedArgs &a, u32 sj, u32 sk
             if (!keep) row[sj] = v;
             if (r_ == a.mass_row) new_mass = v;
         }
+        if (a.dep_radius == nullptr && a.dep_volume != nullptr) {
+            // only the "volume" attribute is kept current (Golovin / Linear read it)
+            const double vol = new_mass / a.rho_w;
+            a.dep_volume[sk] = vol;
+            if (!keep) a.dep_volume[sj] = vol;
+        }
         if ((K == KERNEL_GEOMETRIC || K == KERNEL_HYDRODYNAMIC) && a.dep_radius != nullptr) {
             // the attributes derived from the water mass, for the changed super-droplets only
             DependentParams dp;

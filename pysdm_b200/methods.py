@@ -309,12 +309,12 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         args.length_dev = _pi(adaptive.get("length_dev"))
     if dependents is not None:  # see pysdm_b200_fused_args `dep_*`
         args.dep_volume = _pf(dependents.get("volume"))
-        args.dep_radius = _pf(dependents["radius"])
+        args.dep_radius = _pf(dependents.get("radius"))
         args.dep_velocity = _pf(dependents.get("velocity"))
         args.dep_table_b = _pf(dependents.get("table_b"))
         args.dep_table_c = _pf(dependents.get("table_c"))
-        args.dep_radius_scale = float(dependents["radius_scale"])
-        args.dep_radius_exponent = float(dependents["radius_exponent"])
+        args.dep_radius_scale = float(dependents.get("radius_scale", 0.0))
+        args.dep_radius_exponent = float(dependents.get("radius_exponent", 0.0))
         args.dep_table_factor = float(dependents.get("table_factor", 0.0))
         args.dep_radius_max = float(dependents.get("radius_max", float("inf")))
         args.dep_status = _pi(dependents.get("status"))

@@ -42,7 +42,7 @@ class Random:  # pylint: disable=too-few-public-methods
                 and RECORDER.defer("philox_fill", run, {"tensor": data, "seed": seed,
                                                         "call": call}, [data])):
             return
-        if RECORDER.queue or RECORDER.lazy:
+        if RECORDER.busy():
             RECORDER.sync([data])
         run()
 
@@ -62,6 +62,6 @@ class HostReplayRandom:  # pylint: disable=too-few-public-methods
 
     def __call__(self, storage):
         host = self.generator.uniform(0, 1, storage.shape)
-        if RECORDER.queue or RECORDER.lazy:
+        if RECORDER.busy():
             RECORDER.sync([storage.data])
         storage.data.copy_(torch.from_numpy(host).to(DEVICE, non_blocking=False))

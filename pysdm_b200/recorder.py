@@ -69,11 +69,19 @@ class Recorder:  # pylint: disable=too-many-instance-attributes
         self.written = set()   # ... write
         self.lazy = {}         # base pointer -> (tensor, seed, call): Random fills not yet done
         self.scratch = {}      # per cell_start tensor: nf_slot, status, what they were built for
+        # data pointer of a "volume" tensor -> data pointer of the mass tensor it is current for
+        # (a fused launch refreshed it for the super-droplets it changed, nothing wrote either
+        # since): volume_of_water_mass has nothing to do then
+        self.current = {}
         self.n_fused = self.n_replayed = 0
 
     # ---- recording ---------------------------------------------------------------------------
     def active(self):
         return self.enabled and bool(self.queue)
+
+    def busy(self):
+        """something is recorded, pending or being tracked: callers must `sync` what they touch"""
+        return bool(self.queue or self.lazy or self.current)
 
     def defer(self, name, run, args, tensors, written=None):
         """records an operation; `run` executes it eagerly; `written`: the tensors among
@@ -102,6 +110,10 @@ class Recorder:  # pylint: disable=too-many-instance-attributes
         if self.queue and (any(base_ptr(t) in self.touched for t in tensors)
                            or any(base_ptr(t) in self.written for t in reads)):
             self.flush()
+        if self.current and tensors:
+            written = {base_ptr(t) for t in tensors}
+            self.current = {v: (mass, bases) for v, (mass, bases) in self.current.items()
+                            if not bases & written}
         if self.lazy:
             self._materialise(tensors)
             self._materialise(reads)
@@ -120,11 +132,13 @@ class Recorder:  # pylint: disable=too-many-instance-attributes
             op.run()
         if ops:
             self.n_replayed += 1
+            self.current = {}  # (the method-level kernels do not maintain derived attributes)
 
     def flush_all(self):
         """replays the record and performs every pending lazy fill (for code that is about to
         use device pointers directly)"""
         self.flush()
+        self.current = {}
         for tensor, seed, call in self.lazy.values():
             m.philox_uniform(tensor, seed, call)
         self.lazy = {}
@@ -145,6 +159,7 @@ class Recorder:  # pylint: disable=too-many-instance-attributes
             for op in ops:
                 op.run()
             self.n_replayed += 1
+            self.current = {}
 
 
 # one caller thread per process (SURVEY 8b "Threading"): one record

@@ -106,7 +106,7 @@ def _kernel_block(cur, backend):  # pylint: disable=too-many-return-statements,t
     if mass is None or mul_b is None or not _same(mul_b["out"], kt) or mul_b["b"] is not None:
         return None
     return {"kernel": "Golovin", "kernel_a": 0.0, "kernel_b": mul_b["scalar"], "kt": kt,
-            "mass": mass}
+            "mass": mass, "volume": source}
 
 
 def fused_launch(rec, ops):  # pylint: disable=too-many-locals,too-many-return-statements,too-many-branches,too-many-statements
@@ -162,6 +162,8 @@ def fused_launch(rec, ops):  # pylint: disable=too-many-locals,too-many-return-s
         if offset < 0 or offset % (8 * n_sd) or offset // (8 * n_sd) >= n_attr:
             return False
         mass_row = offset // (8 * n_sd)
+        # the launch keeps the "volume" attribute current for the super-droplets it changes
+        kw["dependents"] = {"volume": kb["volume"]}
     # (otherwise the row only matters for the derived attributes, which the stock path recomputes)
     # uniforms: generated in the kernel when both arrays come from recorded device fills
     philox = None
@@ -200,6 +202,12 @@ def fused_launch(rec, ops):  # pylint: disable=too-many-locals,too-many-return-s
     if facts.length < idx.data.numel():  # flagged positions beyond the sorted range stay
         facts.tmp_idx.data[facts.length:] = idx.data[facts.length:]
     idx.data, facts.tmp_idx.data = facts.tmp_idx.data, idx.data
+    if "volume" in kb:
+        rec.current[kb["volume"].data_ptr()] = (
+            kb["mass"].data_ptr(), {kb["volume"].untyped_storage().data_ptr(),
+                                    kb["mass"].untyped_storage().data_ptr()})
+    else:
+        rec.current = {}
     if "seed" in philox:  # the two arrays were never written: fill them if anybody asks
         for f in fills:
             rec.lazy[f["tensor"].untyped_storage().data_ptr()] = (f["tensor"], f["seed"], f["call"])

@@ -179,12 +179,12 @@ class Storage(StorageBase):
     def _touch(self, *others):
         """before this storage's memory is written (and `others` read) outside the record of a
         collision step (pysdm_b200/recorder.py)"""
-        if RECORDER.queue or RECORDER.lazy:
+        if RECORDER.busy():
             RECORDER.sync([self.data], [o for o in others if isinstance(o, torch.Tensor)])
 
     def _peek(self):
         """before this storage's memory is read"""
-        if RECORDER.queue or RECORDER.lazy:
+        if RECORDER.busy():
             RECORDER.sync((), [self.data])
 
     def _ew(self, op, a=None, b=None, scalar=0.0, out=None):
@@ -195,7 +195,7 @@ class Storage(StorageBase):
             _lib.check(_lib.load().pysdm_b200_elementwise(
                 _lib.EW[op], ptr(out), ptr(a), ptr(b), float(scalar), out.numel(), stream()), op)
 
-        if RECORDER.queue or RECORDER.lazy:
+        if RECORDER.busy():
             tensors = [t for t in (out, a, b) if t is not None]
             # in-place `*= += **= /=` on storages a recorded collision step has written are part
             # of the record (e.g. `output *= b` after sum_pair); unrelated ones (the `**= 1/3` of

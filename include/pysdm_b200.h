@@ -515,6 +515,27 @@ int pysdm_b200_migration_unpack(const int64_t *records, int64_t n_rows, const in
                                 int64_t n_attr, int64_t *cell_origin, double *position_in_cell,
                                 int n_dims, int64_t n_sd, void *stream);
 
+/* ---- migration to the two ring-neighbour slabs without host round trips --------------------
+ * (pysdm_b200/migration.py; csrc/migration.cu).  counters (i64[8], device): [0] stayers,
+ * [1] free slots (in/out), [2] new working length (out), [3] status (0 ok; 1 a droplet moved
+ * beyond a neighbour slab: nothing was modified, use the general path; 2 capacity exceeded),
+ * [4]/[5] leavers to rank+1 / rank-1, [6]/[7] arrivals.  send / recv: [2, cap + 1, R] records,
+ * row 0 of each buffer = header (word 0 = count). */
+size_t pysdm_b200_migration_split_workspace_bytes(int64_t length);
+int pysdm_b200_migration_split(const int64_t *idx, int64_t length, int64_t *idx_out, int64_t *dest,
+                               int64_t *cell_id, const int64_t *cell_origin,
+                               const double *position_in_cell, int64_t *multiplicity,
+                               const double *attributes, int64_t n_attr, int64_t n_sd, int n_dims,
+                               const int64_t *host_grid, int64_t rank, int64_t world, int64_t *send,
+                               int64_t *leavers, int64_t cap, int64_t *free_stack,
+                               int64_t *counters, void *ws, size_t ws_bytes, void *stream);
+int pysdm_b200_migration_merge(const int64_t *recv, int64_t cap, int64_t *idx_out,
+                               int64_t *multiplicity, double *attributes, int64_t n_attr,
+                               int64_t *cell_origin, double *position_in_cell, int64_t *cell_id,
+                               int64_t n_sd, int n_dims, const int64_t *host_grid, int64_t rank,
+                               int64_t world, const int64_t *free_stack, int64_t *counters,
+                               void *stream);
+
 /* PYSDM_B200_H_END_OF_METHOD_LEVEL -- fused step and later additions follow */
 
 #ifdef __cplusplus

@@ -87,6 +87,11 @@ SIGNATURES = {
     "pysdm_b200_migration_destination": (INT, (P, P, P, P, I64, I64, INT, P, I64, P)),
     "pysdm_b200_migration_pack": (INT, (P, I64, P, I64, I64, P, P, I64, P, P, INT, I64, P)),
     "pysdm_b200_migration_unpack": (INT, (P, I64, P, P, P, P, I64, P, P, INT, I64, P)),
+    "pysdm_b200_migration_split_workspace_bytes": (SIZE, (I64,)),
+    "pysdm_b200_migration_split": (
+        INT, (P, I64, P, P, P, P, P, P, P, I64, I64, INT, P, I64, I64, P, P, I64, P, P, P, SIZE, P)),
+    "pysdm_b200_migration_merge": (
+        INT, (P, I64, P, P, P, I64, P, P, P, I64, INT, P, I64, I64, P, P, P)),
     "pysdm_b200_collision_coalescence_breakup": (
         INT, (P, P, I64, P, I64, I64) + (P,) * 11 + (F64, P, INT, P, P)),
 }

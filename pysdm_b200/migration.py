@@ -10,6 +10,16 @@ droplets whose cell now lies in another rank's slab change hands.
     exchange     (NCCL)  counts, then records: torch.distributed.all_to_all_single (all-to-all-v)
     unpack       (CUDA)  arrivals -> free SD slots, appended to idx
 
+With slabs of rows and Courant numbers below one droplets only ever move to the two ring
+neighbours; `migrate()` therefore first runs a device-driven neighbour exchange with NO host
+round trip before the data is where it belongs (csrc/migration.cu, second half): one 64-bit
+scan gives the stable positions of stayers / up-movers / down-movers, the leavers are packed
+into two fixed-capacity buffers whose first row carries the count, two send/recv pairs move
+them (NCCL, fixed sizes: no count exchange), the arrivals are merged from a device free stack;
+the host reads the new working length once, at the end.  Droplets that moved farther (thin
+slabs) are left in place by that pass and handled by the general all-to-all-v path above,
+which all ranks enter together when any rank saw such a droplet (one all-reduced flag).
+
 The reference is single-process (no counterpart to cite); the data model is its own
 (PySDM/impl/particle_attributes.py: SoA by SD number + `idx` + working length).  `exchange`
 is plain torch.distributed and runs with gloo on CPU tensors too, which is how the routing
@@ -17,6 +27,7 @@ logic is tested without GPUs (tests/test_sharding.py); pack/unpack have no CPU p
 """
 
 import ctypes
+import os
 
 import torch
 
@@ -52,7 +63,8 @@ class SlabMigrator:  # pylint: disable=too-many-instance-attributes
     free."""
 
     def __init__(self, *, grid, rank, world, multiplicity, attributes, cell_origin,
-                 position_in_cell, cell_id, idx, length, exchange_fn=exchange):
+                 position_in_cell, cell_id, idx, length, exchange_fn=exchange,
+                 neighbour_exchange_fn=None, capacity=None):
         self.grid = tuple(int(n) for n in grid)
         self.rank, self.world = int(rank), int(world)
         self.rows = cell_range(self.grid[0], self.rank, self.world)
@@ -68,11 +80,35 @@ class SlabMigrator:  # pylint: disable=too-many-instance-attributes
         self.order = torch.empty(self.n_cap, dtype=torch.int64, device=dev)
         self.rank_idx = torch.arange(self.world, dtype=torch.int64, device=dev)
         self.dest_start = torch.zeros(self.world + 1, dtype=torch.int64, device=dev)
-        # free slots: everything idx[:length] does not reference
+        # free slots: everything idx[:length] does not reference; kept as a stack on the device
         used = torch.zeros(self.n_cap, dtype=torch.bool, device=dev)
         used[idx[:self.length]] = True
+        self.free_stack = torch.zeros(self.n_cap, dtype=torch.int64, device=dev)
+        self.n_free = 0
         self.free = torch.nonzero(~used).reshape(-1)
         self.n_sent = self.n_received = 0
+        # neighbour exchange: records per direction, buffers, device counters (csrc/migration.cu)
+        self.neighbour_exchange_fn = neighbour_exchange_fn or neighbour_exchange
+        # (a few per cent of the population per direction; exceeding it is reported, not silent)
+        self.cap = int(capacity or os.environ.get("PYSDM_MIG_CAP") or max(4096, self.n_cap // 64))
+        self.send = torch.zeros((2, self.cap + 1, self.n_words), dtype=torch.int64, device=dev)
+        self.recv = torch.zeros_like(self.send)
+        self.leavers = torch.zeros((2, self.cap), dtype=torch.int64, device=dev)
+        self.idx_out = torch.zeros(self.n_cap, dtype=torch.int64, device=dev)
+        self.counters = torch.zeros(8, dtype=torch.int64, device=dev)
+        self.counters_host = torch.zeros(8, dtype=torch.int64).pin_memory()
+        self.far = torch.zeros(1, dtype=torch.int64, device=dev)
+        self._ws = None
+        self.n_general = 0  # times the general path had to run
+
+    @property
+    def free(self):
+        return self.free_stack[:self.n_free]
+
+    @free.setter
+    def free(self, slots):
+        self.n_free = int(slots.numel())
+        self.free_stack[:self.n_free] = slots
 
     @property
     def n_local_cells(self):
@@ -92,9 +128,70 @@ class SlabMigrator:  # pylint: disable=too-many-instance-attributes
         """one exchange; returns the new working length.  Afterwards idx[:length] holds the
         stayers in their previous relative order followed by the arrivals (by source rank),
         cell_id is valid (slab-local) for all of them, and the population is NOT sorted by cell."""
+        self.split()
+        self.neighbour_exchange_fn(self.send, self.recv, self.rank, self.world)
+        if self.merge(all_reduce_far=self.world > 1):  # some rank saw a far mover: all ranks
+            self.migrate_general()                     # run the general path on what is left
+        return self.length
+
+    def migrate_general(self):
+        """the all-to-all-v path: any destination, two host round trips"""
+        self.n_general += 1
         records, send_counts = self.pack()
         recv, _ = self.exchange_fn(records, send_counts)
         return self.unpack(recv)
+
+    # ---- neighbour path (no host round trip until the end) -----------------------------------
+    def split(self):
+        """classify + scan + split + pack: the stayers in idx_out, both send buffers filled"""
+        lib, stream = _lib.load(), torch.cuda.current_stream().cuda_stream
+        nbytes = lib.pysdm_b200_migration_split_workspace_bytes(self.n_cap)
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = torch.empty(int(nbytes) + 256, dtype=torch.uint8,
+                                   device=self.multiplicity.device)
+        self.counters.zero_()
+        self.counters[1] = self.n_free
+        grid = (ctypes.c_int64 * self.n_dims)(*self.grid)
+        _lib.check(lib.pysdm_b200_migration_split(
+            self.idx.data_ptr(), int(self.length), self.idx_out.data_ptr(), self.dest.data_ptr(),
+            self.cell_id.data_ptr(), self.cell_origin.data_ptr(),
+            self.position_in_cell.data_ptr(), self.multiplicity.data_ptr(),
+            self.attributes.data_ptr(), self.n_attr, self.n_cap, self.n_dims, grid, self.rank,
+            self.world, self.send.data_ptr(), self.leavers.data_ptr(), self.cap,
+            self.free_stack.data_ptr(), self.counters.data_ptr(), self._ws.data_ptr(),
+            self._ws.numel(), stream), "migration_split")
+
+    def merge(self, all_reduce_far=False):
+        """arrivals (self.recv) into free slots behind the stayers; reads the counters back
+        (the one host synchronisation of the exchange).  Returns True when droplets that moved
+        beyond a neighbour slab are still waiting for the general path (on any rank when
+        `all_reduce_far`)"""
+        lib, stream = _lib.load(), torch.cuda.current_stream().cuda_stream
+        grid = (ctypes.c_int64 * self.n_dims)(*self.grid)
+        _lib.check(lib.pysdm_b200_migration_merge(
+            self.recv.data_ptr(), self.cap, self.idx_out.data_ptr(), self.multiplicity.data_ptr(),
+            self.attributes.data_ptr(), self.n_attr, self.cell_origin.data_ptr(),
+            self.position_in_cell.data_ptr(), self.cell_id.data_ptr(), self.n_cap, self.n_dims,
+            grid, self.rank, self.world, self.free_stack.data_ptr(), self.counters.data_ptr(),
+            stream), "migration_merge")
+        if all_reduce_far:
+            import torch.distributed as dist  # pylint: disable=import-outside-toplevel
+
+            self.far.copy_(self.counters[3:4] & 1)
+            dist.all_reduce(self.far, op=dist.ReduceOp.MAX)
+            self.counters[3:4] |= self.far
+        self.counters_host.copy_(self.counters, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        c = [int(x) for x in self.counters_host]
+        if c[3] & 2:
+            raise RuntimeError(f"rank {self.rank}: migration capacity exceeded (leavers {c[4]} + "
+                               f"{c[5]} of {self.cap} per direction, or no free slot left of "
+                               f"{self.n_cap})")
+        self.length, self.n_free = c[2], c[1]
+        self.idx[:self.length] = self.idx_out[:self.length]
+        self.n_sent += c[4] + c[5]
+        self.n_received += c[6] + c[7]
+        return bool(c[3] & 1)
 
     def pack(self):
         """first half: (records [n_send, R] grouped by destination rank, send_counts)"""
@@ -145,3 +242,36 @@ class SlabMigrator:  # pylint: disable=too-many-instance-attributes
         self.length += n_recv
         self.n_received += n_recv
         return self.length
+
+
+_A2A = {}
+
+
+def neighbour_exchange(send, recv, rank, world, group=None):
+    """the two fixed-size send/recv pairs of the neighbour path: send[0] goes to rank + 1, send[1]
+    to rank - 1 (ring); recv[0] comes from rank - 1 (its send[0]), recv[1] from rank + 1 (its
+    send[1]).  No counts are exchanged: each buffer's first row carries its count."""
+    if world == 1:
+        recv.zero_()
+        return
+    import torch.distributed as dist  # pylint: disable=import-outside-toplevel
+
+    up, down = (rank + 1) % world, (rank - 1) % world
+    if os.environ.get("PYSDM_MIG_EXCHANGE") == "a2a":  # one fixed-size all-to-all instead
+        out = _A2A.get((send.data_ptr(), world))
+        if out is None:
+            out = _A2A[(send.data_ptr(), world)] = (
+                torch.zeros((world,) + tuple(send.shape), dtype=send.dtype, device=send.device),
+                torch.zeros((world,) + tuple(send.shape), dtype=send.dtype, device=send.device))
+        buf_out, buf_in = out
+        buf_out[:, :, 0, 0] = 0  # headers of the unused slots
+        buf_out[up, 0].copy_(send[0])
+        buf_out[down, 1].copy_(send[1])
+        dist.all_to_all_single(buf_in, buf_out, group=group)
+        recv[0].copy_(buf_in[down, 0])
+        recv[1].copy_(buf_in[up, 1])
+        return
+    ops = [dist.P2POp(dist.isend, send[0], up, group), dist.P2POp(dist.irecv, recv[0], down, group),
+           dist.P2POp(dist.isend, send[1], down, group), dist.P2POp(dist.irecv, recv[1], up, group)]
+    for request in dist.batch_isend_irecv(ops):
+        request.wait()

@@ -40,6 +40,46 @@ def test_migration_loopback_three_slabs():
     np.testing.assert_array_equal(sizes, want)
 
 
+@pytest.mark.parametrize("world", (1, 2, 3, 6))
+def test_migration_neighbour_path_loopback(world):
+    """the device-driven neighbour exchange (no host round trip before the data is in place:
+    64-bit scan of the three classes, fixed-capacity buffers with the count in their header,
+    device free stack) on a loopback world; with 6 thin slabs some droplets move farther than a
+    neighbour: they must be left in place, reported, and moved by the general path afterwards"""
+    from .migration_common import Shard, global_population, moved, sort_and_count  # pylint: disable=import-outside-toplevel
+
+    pop = global_population()
+    shards = [Shard(pop, r, world) for r in range(world)]
+    for s in shards:
+        s.displace()
+        s.migrator.split()
+    for dst, s in enumerate(shards):  # what the two send/recv pairs deliver to rank `dst`
+        if world == 1:
+            s.migrator.recv.zero_()
+        else:
+            s.migrator.recv[0].copy_(shards[(dst - 1) % world].migrator.send[0])
+            s.migrator.recv[1].copy_(shards[(dst + 1) % world].migrator.send[1])
+    far = [s.migrator.merge() for s in shards]
+    assert any(far) == (world == 6)
+    if any(far):  # every rank enters the general path together
+        packed = [s.migrator.pack() for s in shards]
+        for dst, s in enumerate(shards):
+            parts = []
+            for src in range(world):
+                records, counts = packed[src]
+                begin = sum(counts[:dst])
+                parts.append(records[begin:begin + counts[dst]])
+            s.migrator.unpack(torch.cat(parts))
+    origin, _ = moved(pop)
+    total = sum(s.check(pop) for s in shards)
+    assert total == pop["multiplicity"].size
+    sent = sum(s.migrator.n_sent for s in shards)
+    assert sent == sum(s.migrator.n_received for s in shards) and (sent > 0 or world == 1)
+    sizes = np.concatenate([sort_and_count(s) for s in shards])
+    want = np.bincount(origin[0] * 6 + origin[1], minlength=66)
+    np.testing.assert_array_equal(sizes, want)
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (NCCL all-to-all)")
 def test_migration_nccl_two_gpus():
     script = os.path.join(os.path.dirname(__file__), "mp_migration_nccl.py")

@@ -197,6 +197,8 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         # slots for the `healthy` flags in flight, the steps whose flags have not been read yet
         self.gate = full(1, 0, i64)
         self.speculation_depth = 8
+        self.substep_speculation = 2  # adaptive loop: sub-steps launched ahead of the read-back
+        self._spec_host = self._cell_idx_ring = None
         self._healthy_slots = torch.ones(self.speculation_depth + 1, dtype=i64).pin_memory()
         self._in_flight = []  # (event, slot), oldest first
         self._slot = 0
@@ -308,6 +310,9 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
                 self.step()
         else:
             self.dt_left.fill_(self.dt)
+            if (self.substep_speculation > 0 and self.fused is not False
+                    and (self.optimized_random or isinstance(self.rnd, Random))):
+                self._adaptive_loop_speculative()
             while self.length != 0:
                 m.sort_by_key(self.cell_idx, self.dt_left)
                 self._cell_idx_identity = False
@@ -339,6 +344,67 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             else:
                 self.sort_by_cell_id()
         self.substep = 0
+
+    def _adaptive_loop_speculative(self):
+        """the adaptive sub-step loop (collision.py:178-190) without a host wait per sub-step:
+        sub-step k + 1 is launched before `healthy` and adaptive_sdm_end's result of sub-step k
+        have been read.  The launch takes its working length from the device word its
+        predecessor wrote (pysdm_b200.h `length_dev` / `adaptive_end`) and does nothing when
+        that is 0 (the loop has ended) or when a predecessor closed the gate (it left zero
+        multiplicities: the host removes them, takes adaptive_sdm_end from the re-sorted
+        population as the reference does, and restarts the chain).  The host bookkeeping of
+        launches that did nothing is rolled back, so the results are those of the
+        step-by-step loop (tests/test_gpu_step.py).  Leaves self.length == 0 when it ran the
+        loop to its end; returns early (length != 0) if the fused step stops applying."""
+        depth = self.substep_speculation
+        ring = depth + 2
+        if self._spec_host is None or self._spec_host.shape[0] != ring:
+            self._spec_host = torch.zeros((ring, 4), dtype=torch.int64).pin_memory()
+            self._cell_idx_ring = [torch.empty_like(self.cell_idx) for _ in range(ring)]
+        end_word = (self._words[1:2], self._words[2:3])
+        k = chain_start = 0
+        pending = []  # (sub-step number, event behind its read-back), oldest first
+        while self.length != 0:
+            cell_idx = self._cell_idx_ring[k % ring]
+            m.sort_by_key(cell_idx, self.dt_left)
+            self.cell_idx, self._cell_idx_identity = cell_idx, False
+            if not self._fused_ok() or self.max_cell > m.fused_max_cell_size():
+                break  # (the streaming step for large cells takes its length from the host)
+            self.step_fused(gated=True, adaptive_end=end_word[k % 2],
+                            length_dev=None if k == chain_start else end_word[(k - 1) % 2])
+            self._spec_host[k % ring].copy_(self._words, non_blocking=True)
+            event = torch.cuda.Event()
+            event.record()
+            pending.append((k, event))
+            k += 1
+            while pending and (len(pending) > depth or pending[0][1].query()):
+                j, event = pending.pop(0)
+                event.synchronize()
+                words = self._spec_host[j % ring]
+                self._check_status(words)
+                if not words[0]:  # sub-step j left zero multiplicities: the later ones were gated
+                    self._rollback(k - 1 - j, self._cell_idx_ring[j % ring])
+                    pending, k = [], j + 1
+                    chain_start = k
+                    self._remove_zero_multiplicities()
+                    self.length = m.adaptive_sdm_end(self.dt_left, self.get_cell_start())
+                    break
+                self.length = int(words[1 + j % 2])
+                if self.length == 0:  # the loop ended with sub-step j: the later ones did nothing
+                    self._rollback(k - 1 - j, self._cell_idx_ring[j % ring])
+                    pending = []
+                    break
+
+    def _rollback(self, n_steps, cell_idx):
+        """host bookkeeping of `n_steps` launches that did nothing"""
+        if n_steps % 2:
+            self.idx, self.tmp_idx = self.tmp_idx, self.idx
+        if isinstance(self.rnd, Random) and not self.optimized_random:
+            self.rnd.call -= 2 * n_steps
+        else:
+            self.substep -= n_steps
+        self.n_fused_steps -= n_steps
+        self.cell_idx = cell_idx
 
     def run(self, steps):
         if self.adaptive or self.substeps != 1:
@@ -433,7 +499,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
                 for _ in range(redo):
                     self.step_async()
 
-    def step_fused(self, gated=False):
+    def step_fused(self, gated=False, adaptive_end=None, length_dev=None):
         """one launch: csrc/fused.cu"""
         kw = {}
         if self.adaptive:
@@ -441,7 +507,8 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
                 "dt_left": self.dt_left, "stats_n_substep": self.stats_n_substep,
                 "stats_dt_min": self.stats_dt_min, "dt_min": self.dt_coal_range[0],
                 "dt_max": self.dt_coal_range[1], "rank_to_cell": self.rank_to_cell,
-                "rank_info": self.rank_info, "adaptive_end": self.adaptive_end}
+                "rank_info": self.rank_info, "length_dev": length_dev,
+                "adaptive_end": self.adaptive_end if adaptive_end is None else adaptive_end}
         if self.dependents is not None:
             kw.update(radius=self.radius, fall_velocity=self.fall_velocity,
                       dependents=self.dependents)

@@ -193,6 +193,32 @@ def test_fused_philox_equals_methods_philox():
     assert sims[0].host("coalescence_rate").sum() > 0
 
 
+@pytest.mark.parametrize("optimized_random", (False, True))
+def test_adaptive_speculation_equals_methods(optimized_random):
+    """the adaptive sub-step loop with sub-steps launched ahead of the host's read-back (device
+    working length, gate, roll-back of launches that did nothing) against the method-level
+    kernels driven sub-step by sub-step, same device Philox stream; small multiplicities make
+    sub-steps leave zero-multiplicity SDs in the middle of the loop"""
+    pop = ragged_population(seed=21, n_cell=300, mean=60, n_attr=2, max_mult=2)
+    common = dict(dt=1.0, dv=1e-8, seed=13, adaptive=True, dt_coal_range=(0.02, 1.0),
+                  optimized_random=optimized_random)
+    sims = [device_sim(kernel=device_kernel(b=GOLOVIN_B), fused=f, **pop, **common)
+            for f in (True, False)]
+    assert sims[0].substep_speculation > 0
+    lengths = set()
+    for step in range(5):
+        for s in sims:
+            s()
+        compare_states(sims[0], _Host(sims[1]), f"speculative adaptive step {step}")
+        np.testing.assert_array_equal(sims[0].host("dt_left"), sims[1].host("dt_left"))
+        np.testing.assert_array_equal(sims[0].host("cell_idx"), sims[1].host("cell_idx"))
+        lengths.add(sims[0].length)
+    assert len(lengths) > 2, "super-droplets were expected to be removed in several steps"
+    assert sims[0].host("stats_n_substep").max() > 5
+    assert sims[0].n_fused_steps >= sims[0].host("stats_n_substep").max()
+    assert sims[0].rnd.call == sims[1].rnd.call
+
+
 def test_speculative_stepping_equals_step_by_step():
     """run() queues fused step k+1 before reading `healthy` of step k (gate word of the fused
     kernel); small multiplicities make steps leave zero-multiplicity SDs, so the gate closes,

@@ -22,8 +22,8 @@ One JSON line on stdout (rank 0):
   per_rank              elapsed time of every rank (N > 1)
   configs               BASELINE configs[0..3] through Builder(backend=B200()) (N = 1 only)
   pysdm_path            configs[4] through PySDM: stock Coalescence and the fused path (N = 1 only)
-  transport             (N > 1) displacement -> NCCL migration -> sort -> adaptive collision loop
-                        with its invariants (configs[3] in kind, sharded over the ranks)
+  transport             displacement -> NCCL migration -> sort -> adaptive collision loop with its
+                        invariants (configs[3] in kind, cells sharded over the N ranks)
 
 `--impl reference` times the CPU restatement of the reference's Numba path (oracle/, kind
 "port") -- and next to it the reference's own Numba backend when it is importable -- on the
@@ -368,7 +368,8 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
     sim.drain()              # `healthy` of the last steps (the reference reads it every step)
     t_end.record()
     barrier()
-    clocks = sampler.summary()
+    n_clock_samples = len(sampler.samples)  # (an NVML query takes milliseconds on this box: the
+    # sampler keeps running through the e2e and transport regions below, all under load)
     my_ms = t_beg.elapsed_time(t_end)
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
     launches = sim.n_launches - launches0
@@ -390,7 +391,7 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
                    "l2": "working set ~0.8 GB per GPU >> 126 MB L2, no flush needed",
                    "sharding": "cells sharded over ranks, no data-path collective",
                    "speculation_depth": sim.speculation_depth},
-        "clocks": clocks, "gpu_launches": launches,
+        "clocks": None, "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,
                      "kernel": "k_fused_step<Golovin, Philox>", "kernel_ms": kernel_ms,
@@ -417,8 +418,12 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
         line["e2e"] = e2e
         if striped is not None:
             line["e2e_striped"] = striped
-    if world > 1 and not args.no_transport:
+    if not args.no_transport:  # (N = 1: the same loop with one slab, the weak-scaling base line)
         line["transport"] = transport_run(args, rank, world, barrier, gather)
+    line["clocks"] = sampler.summary()
+    line["clocks"]["samples_in_first_timed_region"] = n_clock_samples
+    line["clocks"]["window"] = ("value + e2e + transport timed regions (GPU under load "
+                                "throughout); sampled every 0.5 ms through NVML")
     if rank == 0 and world == 1:
         if not args.no_cpu_baseline:
             r = cpu_run(args, 3, 1, min(args.cpu_log2_n_sd, args.log2_n_sd))

@@ -64,6 +64,8 @@ def reduce_products(sums=None, minima=None, maxima=None, group=None):
     Returns the tuple (sums, minima, maxima)."""
     import torch.distributed as dist  # pylint: disable=import-outside-toplevel
 
+    if not dist.is_initialized():  # a single-process run: its own values are the global ones
+        return sums, minima, maxima
     for tensor, op in ((sums, dist.ReduceOp.SUM), (minima, dist.ReduceOp.MIN),
                        (maxima, dist.ReduceOp.MAX)):
         if tensor is not None and tensor.numel():

@@ -14,7 +14,8 @@
  *     asynchronous unless they have a `host_` out-parameter, in which case the stream
  *     is synchronised before returning;
  *   - the return value is 0 or a cudaError_t;
- *   - no entry point allocates: scratch is caller-provided (`*_workspace_bytes`);
+ *   - no entry point allocates: scratch is caller-provided (`*_workspace_bytes`), or, for
+ *     pysdm_b200_shuffle_local_static, a fixed device array inside the library;
  *   - nothing here touches host memory other than `host_*` out-parameters and there is
  *     no CPU implementation behind any symbol.
  */
@@ -44,6 +45,20 @@ int pysdm_b200_shuffle_global(int64_t *idx, int64_t length, const double *u01, v
 int pysdm_b200_shuffle_local(int64_t *idx, const double *u01, const int64_t *cell_start,
                              int64_t n_cell, int64_t length, void *ws, size_t ws_bytes,
                              void *stream);
+
+/* shuffle_local with NO allocation and no caller-provided workspace.  It has no counterpart in
+ * the reference and was added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, serving loops, harnesses that forbid it).
+ * Same kernels and the same result, bit for bit, as pysdm_b200_shuffle_local; the scratch is a
+ * file-scope `static __device__` array in index.cu, sized for at most
+ * PYSDM_B200_SHUFFLE_STATIC_MAX_LENGTH positions (6 MiB, held by every GPU that loads the
+ * library until the process exits).  A longer `length` is rejected with cudaErrorInvalidValue
+ * and a message on stderr.  The first call on a device looks the array's device address up
+ * (cudaGetSymbolAddress; a call with length 0 does only that) -- do it before a graph capture.
+ * All calls share the array: calls that overlap on the GPU (different streams or threads) race. */
+#define PYSDM_B200_SHUFFLE_STATIC_MAX_LENGTH 262144
+int pysdm_b200_shuffle_local_static(int64_t *idx, const double *u01, const int64_t *cell_start,
+                                    int64_t n_cell, int64_t length, void *stream);
 
 /* CellCaretaker.__call__, methods/collisions_methods.py:608-629 with the counting sorts
  * :682-741: stable sort of idx[:length] by cell_idx[cell_id[idx[i]]] into new_idx and

@@ -25,6 +25,7 @@ SIGNATURES = {
     "pysdm_b200_shuffle_workspace_bytes": (SIZE, (I64,)),
     "pysdm_b200_shuffle_global": (INT, (P, I64, P, P, SIZE, P)),
     "pysdm_b200_shuffle_local": (INT, (P, P, P, I64, I64, P, SIZE, P)),
+    "pysdm_b200_shuffle_local_static": (INT, (P, P, P, I64, I64, P)),
     "pysdm_b200_sort_by_cell_workspace_bytes": (SIZE, (I64,)),
     "pysdm_b200_sort_by_cell_id": (INT, (P, P, P, P, I64, P, I64, P, SIZE, P)),
     "pysdm_b200_sort_by_key_workspace_bytes": (SIZE, (I64,)),

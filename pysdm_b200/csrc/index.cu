@@ -3,6 +3,9 @@
 // reference's sequential swap chains), stable sort by cell, sort_by_key,
 // remove_zero_n_or_flagged, cell_id.  C-ABI declared in include/pysdm_b200.h.
 #include "primitives.cuh"
+#include "pysdm_b200.h"
+
+#include <stdio.h>
 
 // ---------------------------------------------------------------------------------
 // identity_index  (reference: impl_numba/methods/index_methods.py:13-20)
@@ -208,6 +211,50 @@ PYSDM_EXPORT int pysdm_b200_shuffle_local(i64 *idx, const double *u01, const i64
                                           void *stream)
 {
     return shuffle_impl<true>(idx, u01, cell_start, n_cell, length, ws, ws_bytes,
+                              (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------
+// shuffle_local for callers that may not allocate (CUDA graph capture, serving loops that
+// forbid cudaMalloc): same kernels, same result bit for bit as pysdm_b200_shuffle_local, with
+// the workspace in a file-scope device array instead of a caller-provided buffer.  No
+// counterpart in the reference.
+//
+// Every GPU that loads the library holds the array (6 MiB) until the process exits.  All calls
+// share it: calls that overlap on the GPU (two streams, two threads) race; `cnt` / `fill` are
+// cleared by shuffle_impl at the start of every call, the rest is fully rewritten before it is
+// read.  In host code the array's NAME is only a host-side stand-in: the device address comes
+// from cudaGetSymbolAddress, looked up once per device with that device current.
+// ---------------------------------------------------------------------------------
+constexpr size_t kShuffleStaticBytes = 24 * (size_t)PYSDM_B200_SHUFFLE_STATIC_MAX_LENGTH + 4096;
+static __device__ __align__(256) unsigned char g_shuffle_static_scratch[kShuffleStaticBytes];
+
+constexpr int kShuffleStaticMaxDevices = 64;
+static void *g_shuffle_static_addr[kShuffleStaticMaxDevices];  // device address, per device
+
+PYSDM_EXPORT int pysdm_b200_shuffle_local_static(i64 *idx, const double *u01, const i64 *cell_start,
+                                                 i64 n_cell, i64 length, void *stream)
+{
+    if (length < 0 || length > (i64)PYSDM_B200_SHUFFLE_STATIC_MAX_LENGTH
+        || shuffle_ws_bytes(length) > kShuffleStaticBytes) {
+        fprintf(stderr,
+                "pysdm_b200_shuffle_local_static: length %lld is outside [0, %lld], the size the "
+                "static scratch array was built for; use pysdm_b200_shuffle_local with a "
+                "caller-provided workspace\n",
+                (long long)length, (long long)PYSDM_B200_SHUFFLE_STATIC_MAX_LENGTH);
+        return (int)cudaErrorInvalidValue;
+    }
+    int device = -1;
+    cudaError_t err = cudaGetDevice(&device);
+    if (err != cudaSuccess) return (int)err;
+    if (device < 0 || device >= kShuffleStaticMaxDevices) return (int)cudaErrorInvalidDevice;
+    void *scratch = g_shuffle_static_addr[device];
+    if (scratch == nullptr) {  // set-up, once per device (a call with length 0 does only this)
+        err = cudaGetSymbolAddress(&scratch, g_shuffle_static_scratch);
+        if (err != cudaSuccess) return (int)err;
+        g_shuffle_static_addr[device] = scratch;
+    }
+    return shuffle_impl<true>(idx, u01, cell_start, n_cell, length, scratch, kShuffleStaticBytes,
                               (cudaStream_t)stream);
 }
 

@@ -105,6 +105,22 @@ def shuffle_local(idx, u01, cell_start, length=None, max_cell=None):
                                        _stream()), "shuffle_local")
 
 
+SHUFFLE_STATIC_MAX_LENGTH = 262144  # PYSDM_B200_SHUFFLE_STATIC_MAX_LENGTH, include/pysdm_b200.h
+
+
+def shuffle_local_static(idx, u01, cell_start, length):
+    """shuffle_local through pysdm_b200_shuffle_local_static: nothing is allocated, here or in
+    the library (the scratch is a fixed device array inside libpysdm_b200.so, shared by all
+    calls: do not overlap them).  `length` = cell_start[-1], known on the host, at most
+    SHUFFLE_STATIC_MAX_LENGTH.  Not in the reference; for callers that may not cudaMalloc"""
+    if not 0 <= int(length) <= SHUFFLE_STATIC_MAX_LENGTH:
+        raise ValueError(f"shuffle_local_static: length {int(length)} exceeds the static scratch "
+                         f"limit of {SHUFFLE_STATIC_MAX_LENGTH} positions; use shuffle_local")
+    check(_lib.load().pysdm_b200_shuffle_local_static(
+        _pi(idx), _pf(u01), _pi(cell_start), cell_start.numel() - 1, int(length), _stream()),
+        "shuffle_local_static")
+
+
 def sort_by_key(idx, attr):
     lib = _lib.load()
     n = attr.numel()

@@ -73,6 +73,14 @@ size_t pysdm_b200_sort_by_key_workspace_bytes(int64_t n);
 int pysdm_b200_sort_by_key(int64_t *idx, const double *attr, int64_t n, void *ws,
                            size_t ws_bytes, void *stream);
 
+/* The same, queued speculatively in the adaptive sub-step loop
+ * (PySDM/dynamics/collisions/collision.py:178-190, where `cell_idx.sort_by_key(dt_left)` opens
+ * every sub-step): nothing happens when the device word *skip_if_zero is 0 -- the working
+ * length the previous sub-step's adaptive_sdm_end left (pysdm_b200_fused_args.adaptive_end),
+ * i.e. the loop has ended.  NULL = always sort.  Looked at only for n <= 65536 keys. */
+int pysdm_b200_sort_by_key_if(int64_t *idx, const double *attr, int64_t n, void *ws,
+                              size_t ws_bytes, const int64_t *skip_if_zero, void *stream);
+
 /* remove_zero_n_or_flagged, methods/collisions_methods.py:664-680: the reference's
  * serial swap-with-last compaction, same surviving order; new length -> *host_new_length */
 size_t pysdm_b200_remove_zero_workspace_bytes(int64_t length);
@@ -214,7 +222,10 @@ typedef struct pysdm_b200_fused_args {
     int32_t reserved;
     int64_t max_cell_size;      /* upper bound of cell_start[c+1]-cell_start[c] (host hint) */
     double *nf_slot;            /* [n_sd / 2] scratch: norm_factor[cell_idx[cell_id[d]]] per pair
-                                   slot d (the factor `normalize` applies, :647-648) */
+                                   slot d (the factor `normalize` applies, :647-648).  Adaptive
+                                   launches over cells of at most pysdm_b200_fused_max_cell_size()
+                                   super-droplets follow that chain in the kernel instead
+                                   (cell_idx changes with every sub-step) and leave it untouched */
     int64_t refresh_nf;         /* != 0: recompute norm_factor and nf_slot first.  Must be set
                                    whenever cell_start, cell_idx, cell_id, timestep or dv changed
                                    since the previous call with the same nf_slot buffer */

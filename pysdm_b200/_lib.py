@@ -30,6 +30,7 @@ SIGNATURES = {
     "pysdm_b200_sort_by_cell_id": (INT, (P, P, P, P, I64, P, I64, P, SIZE, P)),
     "pysdm_b200_sort_by_key_workspace_bytes": (SIZE, (I64,)),
     "pysdm_b200_sort_by_key": (INT, (P, P, I64, P, SIZE, P)),
+    "pysdm_b200_sort_by_key_if": (INT, (P, P, I64, P, SIZE, P, P)),
     "pysdm_b200_remove_zero_workspace_bytes": (SIZE, (I64,)),
     "pysdm_b200_remove_zero_n_or_flagged": (INT, (P, P, I64, I64, P, P, SIZE, P)),
     "pysdm_b200_cell_id": (INT, (P, P, P, I64, I64, P)),

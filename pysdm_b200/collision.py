@@ -366,7 +366,9 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         pending = []  # (sub-step number, event behind its read-back), oldest first
         while self.length != 0:
             cell_idx = self._cell_idx_ring[k % ring]
-            m.sort_by_key(cell_idx, self.dt_left)
+            # (skipped on the device once the predecessor's adaptive_sdm_end came out 0)
+            m.sort_by_key(cell_idx, self.dt_left,
+                          skip_if_zero=None if k == chain_start else end_word[(k - 1) % 2])
             self.cell_idx, self._cell_idx_identity = cell_idx, False
             if not self._fused_ok() or self.max_cell > m.fused_max_cell_size():
                 break  # (the streaming step for large cells takes its length from the host)
@@ -533,7 +535,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             nf_slot=self.nf_slot, refresh_nf=not self.nf_valid, gate=self.gate if gated else None,
             epoch=self._epoch + 1, **kw)
         m.check(err, "fused_collision_step")
-        self.n_launches += 1 if self.nf_valid and not self.adaptive else 3
+        self.n_launches += 2 if self.adaptive else (1 if self.nf_valid else 3)
         self.nf_valid = not self.adaptive  # (cell_idx is re-sorted before every adaptive sub-step)
         # positions beyond the sorted range keep their content (flagged SDs)
         if self.sorted_length < self.n_sd:

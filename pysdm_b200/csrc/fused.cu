@@ -3,6 +3,8 @@
 // batch geometry, dispatch on (collision kernel, uniform source, group size, adaptive).
 #include "fused_kernel.cuh"
 
+#include <stdlib.h>
+
 // ---- pre-pass: norm_factor per cell rank (normalize, collisions_methods.py:639-646) ---------
 // adaptive launches also get, per rank r: the cell id it holds and the parity of
 // cell_start[cell_idx[cell id]] -- the position find_pairs (pair_methods.py:40) counts "even"
@@ -110,13 +112,50 @@ static bool divisor_ok(double b)
     return m > 1e-10 && m < 1e10 && mant != 0x000FFFFFFFFFFFFFull;
 }
 
-static i64 cells_per_batch(i64 max_cell_size, bool &warp)
+// CTAs of k_fused_step that are resident at once on the current device
+static i64 resident_ctas()
+{
+    static int sm_count[64];
+    int device = 0;
+    if (cudaGetDevice(&device) != cudaSuccess || device < 0 || device >= 64) return 148 * PYSDM_MIN_CTAS;
+    if (sm_count[device] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || n <= 0)
+            n = 148;
+        sm_count[device] = n;
+    }
+    return (i64)sm_count[device] * PYSDM_MIN_CTAS;
+}
+
+// Cells per batch (= per warp, or per CTA for cells beyond kWarpPos super-droplets).  The upper
+// bound is what fits the group's shared memory.  Below ~10 waves of CTAs the choice also decides
+// how full the LAST wave is: 2^22 super-droplets in cells of 128 are 512 CTAs of 8 cells per
+// warp on 444 resident slots -- two waves, the second one 15 % full.  So the cost model
+// waves(c) * (c + 1) -- a batch costs its cells plus about one cell of fixed work -- is minimised
+// over the admissible c; results do not depend on the choice (cells are independent, uniforms
+// are addressed by global position).
+static i64 cells_per_batch(i64 max_cell_size, i64 n_cell, bool &warp)
 {
     const i64 mcs = max_cell_size < 1 ? 1 : max_cell_size;
     warp = mcs <= kWarpPos;
     i64 cpb = (warp ? kWarpPos : kCtaPos) / mcs;
     const i64 cap = warp ? kWarpCells : kCtaCells;
-    return cpb > cap ? cap : cpb;
+    cpb = cpb > cap ? cap : cpb;
+    static const char *forced = getenv("PYSDM_B200_CELLS_PER_BATCH");  // tuning experiments only
+    if (forced != nullptr && atoll(forced) >= 1) return atoll(forced) < cpb ? atoll(forced) : cpb;
+    const i64 groups = warp ? kFusedThreads / 32 : 1, slots = resident_ctas();
+    i64 best = cpb, best_cost = -1;
+    for (i64 c = cpb; c >= 1 && c >= cpb / 4; --c) {
+        const i64 n_ctas = ((n_cell + c - 1) / c + groups - 1) / groups;
+        const i64 waves = (n_ctas + slots - 1) / slots;
+        const i64 cost = waves * (c + 1);
+        if (best_cost < 0 || cost < best_cost) {
+            best = c;
+            best_cost = cost;
+        }
+        if (waves > 12) break;  // many waves: the tail no longer matters
+    }
+    return best;
 }
 
 PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *host_args,
@@ -147,12 +186,14 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
         k_fused_norm_factor<<<grid_for(a.n_cell), kThreads, 0, st>>>(
             a.cell_start, a.n_cell, a.norm_factor, a.timestep, a.dv, a.refresh_nf != 0,
             a.rank_to_cell, a.cell_idx, a.rank_info, a.adaptive_end);
-        if (a.n_sd / 2 > 0)
+        // (adaptive sub-steps of the batched kernel follow the chain themselves: cell_idx changes
+        // with every sub-step, so a per-slot cache would be rebuilt as often as it is read)
+        if (a.n_sd / 2 > 0 && (!adaptive || big))
             k_fused_nf_slot<<<grid_for(a.n_sd / 2), kThreads, 0, st>>>(
                 a.cell_id, a.cell_idx, a.norm_factor, a.nf_slot, a.n_sd / 2);
     }
     bool warp;
-    const i64 cpb = cells_per_batch(a.max_cell_size, warp);
+    const i64 cpb = cells_per_batch(a.max_cell_size, a.n_cell, warp);
     a.cells_per_batch = cpb;
     a.reserved = divisor_ok(a.rho_w) ? 1 : 0;
     for (int r = 0; r < 10; ++r) {  // Philox4x32 key schedule (philox.cuh)
@@ -208,7 +249,7 @@ PYSDM_EXPORT int pysdm_b200_shuffle_local_batched(i64 *idx, const double *u01, c
     a.substeps = 1.0;
     a.shuffle_only = 1;
     bool warp;
-    a.cells_per_batch = cells_per_batch(max_cell_size, warp);
+    a.cells_per_batch = cells_per_batch(max_cell_size, n_cell, warp);
     const i64 n_batches = (n_cell + a.cells_per_batch - 1) / a.cells_per_batch;
     return dispatch_fused<KERNEL_CONSTANT_K>(a, n_batches, false, warp, false, false,
                                              (cudaStream_t)stream);

@@ -358,6 +358,17 @@ __device__ __forceinline__ void warp_cell_min(double v, int cell, bool valid, do
     }
 }
 
+// the factor normalize() multiplies prob[d] with: norm_factor[cell_idx[cell_id[d]]], the slot number
+// d used as a PARTICLE number (collisions_methods.py:647-648, quirk A1).  Fixed time step: cached
+// per slot across steps (k_fused_nf_slot).  Adaptive: cell_idx is re-sorted before every sub-step,
+// so the chain is followed here -- consecutive slots share a cell id, the two gathers hit the same
+// line for (nearly) the whole warp.
+template <bool kAdaptive>
+__device__ __forceinline__ double slot_norm_factor(const FusedArgs &a, i64 d)
+{
+    return kAdaptive ? a.norm_factor[a.cell_idx[a.cell_id[d]]] : a.nf_slot[d];
+}
+
 template <int K, bool kPhilox, bool kWarp, bool kAggregate, bool kAdaptive>
 __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(const FusedArgs a)
 {
@@ -405,7 +416,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     if (!a.shuffle_only)
         for (i64 d = n_pairs_active + (i64)blockIdx.x * kFusedThreads + tid; d < a.n_sd / 2;
              d += (i64)gridDim.x * kFusedThreads)
-            a.gamma[d] = prob_nopair * a.nf_slot[d] / a.substeps;
+            a.gamma[d] = prob_nopair * slot_norm_factor<kAdaptive>(a, d) / a.substeps;
 
     const i64 batch = (i64)blockIdx.x * G::kGroups + group;
     const i64 c0 = batch * a.cells_per_batch;
@@ -909,7 +920,8 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
             } else {
                 dflt[h] = default_slot(lp0, v0, lp1 < P);
             }
-            if ((has[h] && !idle[h]) || dflt[h]) nf[h] = nf_b[dl];
+            if ((has[h] && !idle[h]) || dflt[h])
+                nf[h] = slot_norm_factor<true>(a, (base_al >> 1) + (i64)dl);
         }
 #pragma unroll
         for (int h = 0; h < 2; ++h)

@@ -417,8 +417,10 @@ __device__ __forceinline__ u64 warp_reduce_u64(u64 v, int op)  // 0 min, 1 or, 2
 
 __global__ void __launch_bounds__(kSmallSortThreads)
     k_sort_by_key_small(const double *__restrict__ attr, u64 *ka, i64 *va, u64 *kb, i64 *vb,
-                        i64 *__restrict__ idx, int n)
+                        i64 *__restrict__ idx, int n, const i64 *__restrict__ skip_if_zero)
 {
+    // speculative adaptive sub-steps (pysdm_b200_sort_by_key_if): the loop ended before this one
+    if (skip_if_zero != nullptr && *skip_if_zero == 0) return;
     __shared__ u32 hist[kRadixBins][kSmallSortWarps + 1];  // [digit][warp], padded
     __shared__ u32 warp_sums[kSmallSortWarps];
     __shared__ unsigned long long s_min, s_or, s_and;
@@ -597,10 +599,9 @@ static size_t sort_by_key_ws_bytes(i64 n)
 
 PYSDM_EXPORT size_t pysdm_b200_sort_by_key_workspace_bytes(i64 n) { return sort_by_key_ws_bytes(n); }
 
-PYSDM_EXPORT int pysdm_b200_sort_by_key(i64 *idx, const double *attr, i64 n, void *ws,
-                                        size_t ws_bytes, void *stream)
+static int sort_by_key_impl(i64 *idx, const double *attr, i64 n, void *ws, size_t ws_bytes,
+                            const i64 *skip_if_zero, cudaStream_t st)
 {
-    cudaStream_t st = (cudaStream_t)stream;
     if (n <= 0) return 0;
     if (n == 1) {
         k_fill_i64<<<1, 32, 0, st>>>(idx, 0, 1);
@@ -618,9 +619,11 @@ PYSDM_EXPORT int pysdm_b200_sort_by_key(i64 *idx, const double *attr, i64 n, voi
     w += align_up(sizeof(i64) * (size_t)n);
     u32 *scratch = (u32 *)w;
     if (n <= kSmallSortMax) {
-        k_sort_by_key_small<<<1, kSmallSortThreads, 0, st>>>(attr, ka, va, kb, vb, idx, (int)n);
+        k_sort_by_key_small<<<1, kSmallSortThreads, 0, st>>>(attr, ka, va, kb, vb, idx, (int)n,
+                                                             skip_if_zero);
         return LAUNCH_CHECK();
     }
+    // (more keys than one CTA sorts: the skip word is not looked at, the sort always runs)
     k_f64_sort_keys<<<grid_for(n), kThreads, 0, st>>>(attr, ka, va, n);
     for (int p = 0; p < 8; ++p) {
         const bool last = p == 7;
@@ -633,6 +636,22 @@ PYSDM_EXPORT int pysdm_b200_sort_by_key(i64 *idx, const double *attr, i64 n, voi
         vb = tv;
     }
     return LAUNCH_CHECK();
+}
+
+PYSDM_EXPORT int pysdm_b200_sort_by_key(i64 *idx, const double *attr, i64 n, void *ws,
+                                        size_t ws_bytes, void *stream)
+{
+    return sort_by_key_impl(idx, attr, n, ws, ws_bytes, nullptr, (cudaStream_t)stream);
+}
+
+// sort_by_key queued ahead of the read-back that decides whether it is needed (the adaptive
+// sub-step loop, collision.py:178-190: `cell_idx.sort_by_key(dt_left)` opens every sub-step):
+// does nothing when the device word *skip_if_zero -- the working length its predecessor's
+// adaptive_sdm_end left -- is 0, i.e. the loop has ended; idx then keeps its content.
+PYSDM_EXPORT int pysdm_b200_sort_by_key_if(i64 *idx, const double *attr, i64 n, void *ws,
+                                           size_t ws_bytes, const i64 *skip_if_zero, void *stream)
+{
+    return sort_by_key_impl(idx, attr, n, ws, ws_bytes, skip_if_zero, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------

@@ -121,12 +121,18 @@ def shuffle_local_static(idx, u01, cell_start, length):
         "shuffle_local_static")
 
 
-def sort_by_key(idx, attr):
+def sort_by_key(idx, attr, skip_if_zero=None):
+    """`skip_if_zero`: device int64 word; the sort does nothing when it holds 0 (speculative
+    adaptive sub-steps: the working length the previous sub-step left)"""
     lib = _lib.load()
     n = attr.numel()
     ws = WS.dev("sort_by_key", lib.pysdm_b200_sort_by_key_workspace_bytes(n), idx.device)
-    check(lib.pysdm_b200_sort_by_key(_pi(idx), _pf(attr), n, _p(ws), ws.numel(), _stream()),
-          "sort_by_key")
+    if skip_if_zero is None:
+        check(lib.pysdm_b200_sort_by_key(_pi(idx), _pf(attr), n, _p(ws), ws.numel(), _stream()),
+              "sort_by_key")
+    else:
+        check(lib.pysdm_b200_sort_by_key_if(_pi(idx), _pf(attr), n, _p(ws), ws.numel(),
+                                            _pi(skip_if_zero), _stream()), "sort_by_key_if")
 
 
 def remove_zero_n_or_flagged(multiplicity, idx, length):

@@ -804,3 +804,70 @@ def test_recorded_stock_dynamic_equals_eager(pysdm, kernel):
         assert RECORDER.n_fused == fused0 and RECORDER.n_replayed > replayed0
     else:
         assert RECORDER.n_fused - fused0 == 10 and RECORDER.n_replayed == replayed0
+
+
+def test_vtk_exporter_attributes_equal_numba(pysdm, tmp_path, monkeypatch):
+    """SURVEY 8(f)4, exporters: the reference's `VTKExporter.export_attributes`
+    (PySDM/exporters/vtk_exporter.py:62-110) run UNCHANGED over a particulator on the B200
+    backend -- it downloads every attribute with `to_ndarray(raw=True)` -- hands the writer
+    the same payload as over the Numba backend after the same coalescence steps (pyevtk is not
+    in the image: its `pointsToVTK` is replaced by a recorder of what it is given).
+    `export_products` / the netCDF exporter write products, which are outside the path (8f)."""
+    from PySDM import Builder, Formulae  # pylint: disable=import-outside-toplevel
+    from PySDM.backends import CPU  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics import Coalescence  # pylint: disable=import-outside-toplevel
+    from PySDM.dynamics.collisions.collision_kernels import Golovin  # pylint: disable=import-outside-toplevel
+    from PySDM.environments import Box  # pylint: disable=import-outside-toplevel
+    from PySDM.exporters import vtk_exporter  # pylint: disable=import-outside-toplevel
+    from PySDM.impl.mesh import Mesh  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import B200, FusedCoalescence  # pylint: disable=import-outside-toplevel
+
+    grid, per_cell = (6, 5), 64
+    n_sd = grid[0] * grid[1] * per_cell
+    rng = np.random.default_rng(62)
+    cell = np.arange(n_sd, dtype=np.int64) // per_cell
+    attributes = {
+        "volume": rng.exponential(4 / 3 * np.pi * 30.531e-6 ** 3, n_sd),
+        "multiplicity": rng.integers(1, 2 ** 22, n_sd).astype(np.int64),
+        "cell id": cell, "cell origin": np.stack([cell // grid[1], cell % grid[1]]),
+        "position in cell": rng.uniform(0, 1, (2, n_sd))}
+
+    written = []
+    monkeypatch.setattr(vtk_exporter, "pointsToVTK",
+                        lambda path, x, y, z, data: written.append((path, x, y, z, dict(data))))
+
+    def export(backend, dynamic):
+        env = Box(dv=1e6, dt=1.0)
+        env.mesh = Mesh(grid, size=(60.0, 50.0), dv=1e6)
+        builder = Builder(n_sd=n_sd, backend=backend, environment=env)
+        builder.add_dynamic(dynamic(collision_kernel=Golovin(b=1.5e3)))
+        particulator = builder.build(attributes={k: v.copy() for k, v in attributes.items()},
+                                     products=())
+        exporter = vtk_exporter.VTKExporter(path=str(tmp_path))
+        out = []
+        for _ in range(2):
+            particulator.run(2)
+            exporter.export_attributes(particulator)
+            out.append(written.pop())
+        assert not written
+        return out
+
+    fkw = dict(fastmath=False, seed=62)
+    ref = export(CPU(Formulae(**fkw)), Coalescence)
+    for dynamic in (Coalescence, FusedCoalescence):
+        sut = export(B200(Formulae(**fkw), host_rng=True), dynamic)
+        for (path_r, *xyz_r, data_r), (path_s, *xyz_s, data_s) in zip(ref, sut):
+            assert path_s == path_r and sorted(data_s) == sorted(data_r)
+            assert {"multiplicity", "cell id", "cell origin[0]", "position in cell[1]",
+                    "water mass"} <= set(data_s)
+            for a, b in zip(xyz_r, xyz_s):
+                np.testing.assert_array_equal(a, b)
+            for key, expected in data_r.items():
+                got = data_s[key]
+                assert got.dtype == expected.dtype and got.shape == expected.shape, key
+                assert got.flags["C_CONTIGUOUS"] or got.flags["F_CONTIGUOUS"], key
+                if expected.dtype.kind == "f":  # north_star: attributes within 1e-12 relative
+                    np.testing.assert_allclose(got, expected, rtol=1e-12, atol=0, err_msg=key)
+                else:
+                    np.testing.assert_array_equal(got, expected, err_msg=key)

@@ -286,6 +286,9 @@ typedef struct pysdm_b200_fused_args {
                                     (adaptive loop); 0 = `length` */
     int64_t skip_coalescence;    /* != 0: stop after compute_gamma (breakup: pysdm_b200_fused_breakup
                                     takes over) */
+    int64_t prepass_done;        /* adaptive, != 0: pysdm_b200_adaptive_presort sorted cell_idx for
+                                    this sub-step and zeroed *adaptive_end, norm_factor is valid:
+                                    no pre-pass launch here, rank_info is neither read nor written */
 } pysdm_b200_fused_args;
 
 int64_t pysdm_b200_fused_max_cell_size(void);
@@ -298,6 +301,23 @@ int pysdm_b200_shuffle_local_batched(int64_t *idx, const double *u01, const int6
                                      int64_t n_cell, int64_t n_sd, int64_t max_cell_size,
                                      int64_t *status, void *stream);
 int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *host_args, void *stream);
+
+/* Opens one sub-step of the adaptive loop (PySDM/dynamics/collisions/collision.py:181,
+ * `cell_idx.sort_by_key(dt_left)`, index_methods.py:46-48) with ONE launch between two launches
+ * of the fused step: the sort of the n_cell keys, which also zeroes *adaptive_end (the word the
+ * fused sub-step accumulates adaptive_sdm_end in).  Follow it with
+ * pysdm_b200_fused_collision_step(prepass_done = 1): that launch then derives, per rank of
+ * cell_start, the cell id and the parity find_pairs counts from under the re-sorted cell_idx
+ * (pair_methods.py:40) itself instead of reading rank_info, and takes norm_factor as it is.
+ * norm_factor != NULL: the per-cell factors of normalize (collisions_methods.py:639-646) are
+ * (re)computed from cell_start, timestep and dv first -- needed once after every sort by cell.
+ * `skip_if_zero` as in pysdm_b200_sort_by_key_if (a skipped launch still zeroes *adaptive_end, so
+ * the sub-steps queued behind it do nothing either);
+ * ws: pysdm_b200_sort_by_key_workspace_bytes(n_cell). */
+int pysdm_b200_adaptive_presort(int64_t *cell_idx, const double *dt_left, int64_t n_cell, void *ws,
+                                size_t ws_bytes, const int64_t *skip_if_zero,
+                                const int64_t *cell_start, double *norm_factor, double timestep,
+                                double dv, int64_t *adaptive_end, void *stream);
 
 /* ---- fused breakup: the second half of a Collision.step() with enable_breakup ---------------
  * (PySDM/dynamics/collisions/collision.py:206-234).  pysdm_b200_fused_collision_step with
@@ -489,6 +509,20 @@ int pysdm_b200_calculate_displacement(int dim, int n_dims, int implicit_in_space
                                       const int64_t *host_courant_shape,
                                       const int64_t *cell_origin, const double *position_in_cell,
                                       int64_t n_sd, double n_substeps, void *stream);
+/* Displacement.__call__ without sedimentation (PySDM/dynamics/displacement.py:103-153) in one
+ * launch: calculate_displacement for every dimension (from the positions before the update, as
+ * the separate calls see them), update_position (`position_in_cell += displacement`),
+ * update_cell_origin (`floor`, `cell_origin +=`, `position_in_cell -=`) and boundary_condition
+ * (`cell_origin %= grid`, numpy's modulo) -- per super-droplet, same operations in the same
+ * order, so bit-identical to the seven separate calls; `displacement` is written as well.
+ * host_courant[n_dims]: HOST array of the device pointers of the Courant components;
+ * host_courant_shapes[n_dims * n_dims]: HOST, row `dim` = the shape of component `dim`;
+ * host_grid[n_dims]: HOST, the grid. */
+int pysdm_b200_displacement_step(int n_dims, int implicit_in_space, double *displacement,
+                                 const double *const *host_courant,
+                                 const int64_t *host_courant_shapes, const int64_t *host_grid,
+                                 int64_t *cell_origin, double *position_in_cell, int64_t n_sd,
+                                 double n_substeps, void *stream);
 /* flag_precipitated, :155-186, 208-238: the *_z pointers are the LAST rows of the [n_dims, n_sd]
  * arrays; flagged positions of idx get idx_len (= n_sd); rainfall_mass = device f64[1] */
 int pysdm_b200_flag_precipitated(const int64_t *cell_origin_z, const double *position_in_cell_z,

@@ -48,8 +48,9 @@ def wrap(tensor, dtype):
 
 class TransportLoop:  # pylint: disable=too-many-instance-attributes
     def __init__(self, rank, world, *, rows_per_gpu=64, cols=512, sd_per_cell=128,
-                 kernel="geometric"):
+                 kernel="geometric", fused_displacement=True):
         self.rank, self.world = rank, world
+        self.fused_displacement = fused_displacement
         dev = self.dev = torch.device("cuda")
         grid = self.grid = (rows_per_gpu * world, cols)
         self.rows = rows = cell_range(grid[0], rank, world)
@@ -120,15 +121,20 @@ class TransportLoop:  # pylint: disable=too-many-instance-attributes
         sim, mig = self.sim, self.mig
         if timed:
             self.ev[0].record()
-        for dim in range(2):  # Particulator.calculate_displacement, particulator.py:428-440
-            m.calculate_displacement(dim, self.displacement, self.courant[dim], self.cell_origin,
-                                     self.position, 1)
-        pos, org = wrap(self.position, Storage.FLOAT), wrap(self.cell_origin, Storage.INT)
-        pos += wrap(self.displacement, Storage.FLOAT)  # Displacement.update_position
-        self.floor_tmp.floor(pos)                      # Displacement.update_cell_origin
-        org += self.floor_tmp
-        pos -= self.floor_tmp
-        org %= self.grid_storage                       # Displacement.boundary_condition
+        if self.fused_displacement:
+            # Displacement.__call__ (dynamics/displacement.py:103-153) in one launch
+            m.displacement_step(self.displacement, self.courant, self.cell_origin, self.position,
+                                self.grid, 1)
+        else:  # the same as the reference issues it: seven passes
+            for dim in range(2):  # Particulator.calculate_displacement, particulator.py:428-440
+                m.calculate_displacement(dim, self.displacement, self.courant[dim],
+                                         self.cell_origin, self.position, 1)
+            pos, org = wrap(self.position, Storage.FLOAT), wrap(self.cell_origin, Storage.INT)
+            pos += wrap(self.displacement, Storage.FLOAT)  # Displacement.update_position
+            self.floor_tmp.floor(pos)                      # Displacement.update_cell_origin
+            org += self.floor_tmp
+            pos -= self.floor_tmp
+            org %= self.grid_storage                       # Displacement.boundary_condition
         if timed:
             self.ev[1].record()
         mig.idx, mig.length = sim.idx, sim.length
@@ -194,8 +200,8 @@ def bench_entry(rank, world, steps, barrier, gather, **loop_kw):
     n_total = int(t1[2])
     mass_err = float(abs(t1[1] - t0[1]) / t0[1])
     return {
-        "loop": "displacement + migration (NCCL all-to-all-v) + derived attributes + sort by "
-                "cell + collision sub-steps",
+        "loop": "displacement (one launch) + migration (device-driven neighbour exchange, NCCL "
+                "send/recv) + derived attributes + sort by cell + collision sub-steps",
         "collision": loop.what, "grid": list(loop.grid), "super_droplets": n_total,
         "super_droplets_per_gpu": loop.n0, "steps": steps, "ms_per_step": ms / steps,
         "sd_steps_per_s": n_total * steps / (ms * 1e-3), "per_rank_ms": per_rank,

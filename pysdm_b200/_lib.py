@@ -31,6 +31,7 @@ SIGNATURES = {
     "pysdm_b200_sort_by_key_workspace_bytes": (SIZE, (I64,)),
     "pysdm_b200_sort_by_key": (INT, (P, P, I64, P, SIZE, P)),
     "pysdm_b200_sort_by_key_if": (INT, (P, P, I64, P, SIZE, P, P)),
+    "pysdm_b200_adaptive_presort": (INT, (P, P, I64, P, SIZE, P, P, P, F64, F64, P, P)),
     "pysdm_b200_remove_zero_workspace_bytes": (SIZE, (I64,)),
     "pysdm_b200_remove_zero_n_or_flagged": (INT, (P, P, I64, I64, P, P, SIZE, P)),
     "pysdm_b200_cell_id": (INT, (P, P, P, I64, I64, P)),
@@ -82,6 +83,7 @@ SIGNATURES = {
     "pysdm_b200_spectrum_moments": (
         INT, (P, P, P, P, P, P, I64, F64, INT, P, I64, P, P, F64, INT, I64, P)),
     "pysdm_b200_calculate_displacement": (INT, (INT, INT, INT, P, P, P, P, P, I64, F64, P)),
+    "pysdm_b200_displacement_step": (INT, (ctypes.c_int, ctypes.c_int, P, P, P, P, P, P, I64, F64, P)),
     "pysdm_b200_flag_precipitated": (INT, (P, P, P, P, P, I64, I64, P, F64, P, P, P)),
     "pysdm_b200_flag_out_of_column": (INT, (P, P, P, I64, I64, P, F64, P)),
     "pysdm_b200_seeding_workspace_bytes": (SIZE, (I64,)),
@@ -121,7 +123,8 @@ class FusedArgs(ctypes.Structure):
            ("dep_volume", P), ("dep_radius", P), ("dep_velocity", P), ("dep_table_b", P),
            ("dep_table_c", P), ("dep_radius_scale", F64), ("dep_radius_exponent", F64),
            ("dep_table_factor", F64), ("dep_radius_max", F64), ("dep_status", P),
-           ("ws", P), ("ws_bytes", U64), ("sorted_length", I64), ("skip_coalescence", I64)])
+           ("ws", P), ("ws_bytes", U64), ("sorted_length", I64), ("skip_coalescence", I64),
+           ("prepass_done", I64)])
 
 
 class BreakupArgs(ctypes.Structure):

@@ -150,6 +150,18 @@ class B200(BackendMethods):  # pylint: disable=too-many-public-methods
         self._identity_ptrs.discard(idx.data.data_ptr())
         self._versions[idx.data.data_ptr()] = self._versions.get(idx.data.data_ptr(), 0) + 1
 
+    def adaptive_presort(self, cell_idx, dt_left, *, cell_start, norm_factor, timestep, dv,
+                         adaptive_end):
+        """`cell_idx.sort_by_key(dt_left)` of the adaptive loop (collision.py:181) opening a fused
+        sub-step, one launch (pysdm_b200_adaptive_presort); `norm_factor`: None when the
+        per-cell factors of normalize() are valid for the current sort by cell"""
+        RECORDER.flush_all()
+        m.adaptive_presort(cell_idx.data, dt_left.data, cell_start=cell_start.data,
+                           norm_factor=None if norm_factor is None else norm_factor.data,
+                           timestep=timestep, dv=dv, adaptive_end=adaptive_end)
+        self._identity_ptrs.discard(cell_idx.data.data_ptr())
+        self._versions[cell_idx.data.data_ptr()] = self._versions.get(cell_idx.data.data_ptr(), 0) + 1
+
     @staticmethod
     def remove_zero_n_or_flagged(multiplicity, idx, length):  # collisions_methods.py:664-680
         return m.remove_zero_n_or_flagged(multiplicity, idx, int(length))

@@ -144,7 +144,8 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.max_cell = None
         # words the host reads back after a step: [0] healthy, [1:3] the fused adaptive
         # sub-step's adaptive_sdm_end result (pysdm_b200.h `adaptive_end`)
-        self._words = full(4, 0, i64)
+        # healthy, end, end, status, end, end, end, end, gate
+        self._words = full(9, 0, i64)
         self.healthy = self._words[0:1]
         self.healthy.fill_(1)
         self.adaptive_end = self._words[1:3]
@@ -166,6 +167,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.status = self._words[3:4]  # fused step: a batch of cells did not fit (wrong hint)
         self.nf_slot = full(n_pairs, nan, f64)  # fused step: normalize factor per pair slot
         self.nf_valid = False  # False after anything that changes cell_start/cell_idx/cell_id
+        self.norm_factor_valid = False  # norm_factor[] matches cell_start (adaptive presort)
         # RandomGeneratorOptimizer.register
         self.optimized_random = optimized_random
         shift = math.ceil(dt / dt_coal_range[0]) if optimized_random else 0
@@ -192,10 +194,10 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.n_fused_steps = 0
         self._epoch = 0
         self._healthy_host = torch.ones(1, dtype=i64).pin_memory()
-        self._words_host = torch.zeros(4, dtype=i64).pin_memory()
+        self._words_host = torch.zeros(9, dtype=i64).pin_memory()
         # speculative stepping (step_async): gate word of the fused kernel, a ring of pinned
         # slots for the `healthy` flags in flight, the steps whose flags have not been read yet
-        self.gate = full(1, 0, i64)
+        self.gate = self._words[8:9]
         self.speculation_depth = 8
         self.substep_speculation = 2  # adaptive loop: sub-steps launched ahead of the read-back
         self._spec_host = self._cell_idx_ring = None
@@ -232,7 +234,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self._sort_identity = self._cell_idx_identity
         self.sorted_length = self.length  # = cell_start[-1], kept on the host
         self.max_cell = None
-        self.nf_valid = False
+        self.nf_valid = self.norm_factor_valid = False
 
     def reset_permutation(self):
         """after the caller has overwritten multiplicity / attributes / cell_id in place:
@@ -314,13 +316,13 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
                     and (self.optimized_random or isinstance(self.rnd, Random))):
                 self._adaptive_loop_speculative()
             while self.length != 0:
-                m.sort_by_key(self.cell_idx, self.dt_left)
+                prepass_done = self._open_substep(self.cell_idx, self.adaptive_end, None)
                 self._cell_idx_identity = False
                 if self._fused_ok():
                     # the launch also leaves adaptive_sdm_end's result next to `healthy`: one
                     # read-back per sub-step (valid unless SDs were removed: the reference then
                     # re-sorts by cell before adaptive_sdm_end looks at cell_start)
-                    self.step_fused()
+                    self.step_fused(prepass_done=prepass_done)
                     self._words_host.copy_(self._words, non_blocking=True)
                     torch.cuda.current_stream().synchronize()
                     self._check_status(self._words_host)
@@ -359,43 +361,76 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         depth = self.substep_speculation
         ring = depth + 2
         if self._spec_host is None or self._spec_host.shape[0] != ring:
-            self._spec_host = torch.zeros((ring, 4), dtype=torch.int64).pin_memory()
+            self._spec_host = torch.zeros((ring, 9), dtype=torch.int64).pin_memory()
             self._cell_idx_ring = [torch.empty_like(self.cell_idx) for _ in range(ring)]
-        end_word = (self._words[1:2], self._words[2:3])
+            self._side_stream = torch.cuda.Stream()
+        # adaptive_sdm_end's result of sub-step k lives in its own word of a ring as long as the
+        # ring of read-backs: the word is rewritten `ring` sub-steps later, by when the host has
+        # read it -- so the read-back can leave the main stream (a side stream copies the words
+        # once the launch is done) and no copy sits between two sub-steps
+        assert ring <= 6
+        slots = (1, 2, 4, 5, 6, 7)[:ring]
+        end_word = [self._words[i:i + 1] for i in slots]
+        main, side = torch.cuda.current_stream(), self._side_stream
         k = chain_start = 0
         pending = []  # (sub-step number, event behind its read-back), oldest first
         while self.length != 0:
             cell_idx = self._cell_idx_ring[k % ring]
             # (skipped on the device once the predecessor's adaptive_sdm_end came out 0)
-            m.sort_by_key(cell_idx, self.dt_left,
-                          skip_if_zero=None if k == chain_start else end_word[(k - 1) % 2])
+            prepass_done = self._open_substep(
+                cell_idx, end_word[k % ring],
+                None if k == chain_start else end_word[(k - 1) % ring])
             self.cell_idx, self._cell_idx_identity = cell_idx, False
             if not self._fused_ok() or self.max_cell > m.fused_max_cell_size():
                 break  # (the streaming step for large cells takes its length from the host)
-            self.step_fused(gated=True, adaptive_end=end_word[k % 2],
-                            length_dev=None if k == chain_start else end_word[(k - 1) % 2])
-            self._spec_host[k % ring].copy_(self._words, non_blocking=True)
+            self.step_fused(gated=True, adaptive_end=end_word[k % ring],
+                            length_dev=None if k == chain_start else end_word[(k - 1) % ring],
+                            prepass_done=prepass_done)
+            launched = torch.cuda.Event()
+            launched.record(main)
             event = torch.cuda.Event()
-            event.record()
-            pending.append((k, event))
+            with torch.cuda.stream(side):
+                side.wait_event(launched)
+                self._spec_host[k % ring].copy_(self._words, non_blocking=True)
+                event.record(side)
+            pending.append((k, event, self._epoch))
             k += 1
             while pending and (len(pending) > depth or pending[0][1].query()):
-                j, event = pending.pop(0)
+                j, event, epoch = pending.pop(0)
                 event.synchronize()
                 words = self._spec_host[j % ring]
                 self._check_status(words)
-                if not words[0]:  # sub-step j left zero multiplicities: the later ones were gated
+                # (the copy may have been taken while later sub-steps were running: the gate
+                # holds the epoch of the launch that closed it, which tells whose zeros these are)
+                if words[8] != 0 and words[8] <= epoch:
+                    # sub-step j left zero multiplicities: the later ones were gated
                     self._rollback(k - 1 - j, self._cell_idx_ring[j % ring])
                     pending, k = [], j + 1
                     chain_start = k
                     self._remove_zero_multiplicities()
                     self.length = m.adaptive_sdm_end(self.dt_left, self.get_cell_start())
                     break
-                self.length = int(words[1 + j % 2])
+                self.length = int(words[slots[j % ring]])
                 if self.length == 0:  # the loop ended with sub-step j: the later ones did nothing
                     self._rollback(k - 1 - j, self._cell_idx_ring[j % ring])
                     pending = []
                     break
+
+    def _open_substep(self, cell_idx, adaptive_end, skip_if_zero):
+        """`cell_idx.sort_by_key(dt_left)` (collision.py:181).  When the population is sorted by
+        cell and the batched fused step is going to take the sub-step, the same launch also does
+        what is left of that step's pre-pass (pysdm_b200_adaptive_presort): returns True then"""
+        if (self.sorted and self.fused is not False and self.croupier == "local"
+                and getattr(self.kernel, "fused", None) is not None and self.max_cell is not None
+                and self.max_cell <= m.fused_max_cell_size() and self.n_sd < 2 ** 31):
+            m.adaptive_presort(cell_idx, self.dt_left, cell_start=self.cell_start,
+                               norm_factor=None if self.norm_factor_valid else self.norm_factor,
+                               timestep=self.dt, dv=self.dv, adaptive_end=adaptive_end,
+                               skip_if_zero=skip_if_zero)
+            self.norm_factor_valid = True  # (until the next sort by cell)
+            return True
+        m.sort_by_key(cell_idx, self.dt_left, skip_if_zero=skip_if_zero)
+        return False
 
     def _rollback(self, n_steps, cell_idx):
         """host bookkeeping of `n_steps` launches that did nothing"""
@@ -501,11 +536,12 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
                 for _ in range(redo):
                     self.step_async()
 
-    def step_fused(self, gated=False, adaptive_end=None, length_dev=None):
+    def step_fused(self, gated=False, adaptive_end=None, length_dev=None, prepass_done=False):
         """one launch: csrc/fused.cu"""
         kw = {}
         if self.adaptive:
             kw["adaptive"] = {
+                "prepass_done": prepass_done,
                 "dt_left": self.dt_left, "stats_n_substep": self.stats_n_substep,
                 "stats_dt_min": self.stats_dt_min, "dt_min": self.dt_coal_range[0],
                 "dt_max": self.dt_coal_range[1], "rank_to_cell": self.rank_to_cell,

@@ -27,6 +27,16 @@ __global__ void k_fused_norm_factor(const i64 *__restrict__ cell_start, i64 n_ce
     }
 }
 
+int pysdm_fused_prepass(const i64 *cell_start, i64 n_cell, double *norm_factor, double timestep,
+                        double dv, const i64 *rank_to_cell, const i64 *cell_idx, i64 *rank_info,
+                        i64 *adaptive_end, cudaStream_t st)
+{
+    k_fused_norm_factor<<<grid_for(n_cell), kThreads, 0, st>>>(
+        cell_start, n_cell, norm_factor, timestep, dv, true, rank_to_cell, cell_idx, rank_info,
+        adaptive_end);
+    return LAUNCH_CHECK();
+}
+
 // per pair slot d: the factor normalize() multiplies prob[d] with (collisions_methods.py:647-648:
 // norm_factor[cell_idx[cell_id[d]]], d used as a PARTICLE number -- reference quirk A1).  It only
 // changes when cell_start / cell_idx / cell_id / dt / dv change, so it is cached across steps.
@@ -182,7 +192,9 @@ PYSDM_EXPORT int pysdm_b200_fused_collision_step(const pysdm_b200_fused_args *ho
         a.adaptive_end = nullptr;
         a.length_dev = nullptr;
     }
-    if (a.refresh_nf || adaptive) {
+    // (prepass_done: pysdm_b200_adaptive_presort has left norm_factor, rank_info and the zeroed
+    // adaptive_end behind, in the launch that sorted cell_idx)
+    if ((a.refresh_nf || adaptive) && !(adaptive && !big && a.prepass_done)) {
         k_fused_norm_factor<<<grid_for(a.n_cell), kThreads, 0, st>>>(
             a.cell_start, a.n_cell, a.norm_factor, a.timestep, a.dv, a.refresh_nf != 0,
             a.rank_to_cell, a.cell_idx, a.rank_info, a.adaptive_end);

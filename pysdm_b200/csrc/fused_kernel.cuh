@@ -369,6 +369,19 @@ __device__ __forceinline__ double slot_norm_factor(const FusedArgs &a, i64 d)
     return kAdaptive ? a.norm_factor[a.cell_idx[a.cell_id[d]]] : a.nf_slot[d];
 }
 
+// adaptive: per rank r of cell_start, the cell id it holds | parity of cell_start[cell_idx[cell id]]
+// << 62 (the position find_pairs counts "even" from under the re-sorted cell_idx, quirk A2).
+// Prepared per rank by the pre-pass (k_fused_norm_factor), or -- prepass_done: the sub-step was
+// opened by pysdm_b200_adaptive_presort, no pre-pass ran -- followed here: three dependent
+// loads per cell at the head of a batch, spread over all SMs, instead of a launch on the
+// critical path between two sub-steps
+__device__ __forceinline__ i64 rank_info_of(const FusedArgs &a, i64 r)
+{
+    if (!a.prepass_done) return a.rank_info[r];
+    const i64 cid = a.rank_to_cell[r];
+    return cid | ((a.cell_start[a.cell_idx[cid]] & 1) << 62);
+}
+
 template <int K, bool kPhilox, bool kWarp, bool kAggregate, bool kAdaptive>
 __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(const FusedArgs a)
 {
@@ -444,7 +457,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
     // from the second sub-step on) skip the kernel evaluation and its gathers altogether.
     if (kAdaptive)
         for (int c = gt; c < ncb; c += G::kSize) {
-            const i64 info = a.rank_info[c0 + c];
+            const i64 info = rank_info_of(a, c0 + c);
             const i64 cid = info & kCidMask;
             const double s = a.stats_dt_min[cid];
             const bool idle = a.dt_left[cid] == 0.0 && s != s;
@@ -880,7 +893,7 @@ __global__ void __launch_bounds__(kFusedThreads, PYSDM_MIN_CTAS) k_fused_step(co
         i64 rr = c1;
         while (rr < a.n_cell && a.cell_start[rr + 1] == end) ++rr;
         if (rr >= a.n_cell || a.cell_start[rr + 1] - end < 2) return true;
-        return (((i64)end ^ (a.rank_info[rr] >> 62)) & 1) != 0;  // its first SD is not "even"
+        return (((i64)end ^ (rank_info_of(a, rr) >> 62)) & 1) != 0;  // its first SD is not "even"
     };
 
     // ---- pass A ----------------------------------------------------------------------------

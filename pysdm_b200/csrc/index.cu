@@ -4,6 +4,7 @@
 // remove_zero_n_or_flagged, cell_id.  C-ABI declared in include/pysdm_b200.h.
 #include "primitives.cuh"
 #include "pysdm_b200.h"
+#include "sdm_device.cuh"
 
 #include <stdio.h>
 
@@ -417,9 +418,14 @@ __device__ __forceinline__ u64 warp_reduce_u64(u64 v, int op)  // 0 min, 1 or, 2
 
 __global__ void __launch_bounds__(kSmallSortThreads)
     k_sort_by_key_small(const double *__restrict__ attr, u64 *ka, i64 *va, u64 *kb, i64 *vb,
-                        i64 *__restrict__ idx, int n, const i64 *__restrict__ skip_if_zero)
+                        i64 *__restrict__ idx, int n, const i64 *__restrict__ skip_if_zero,
+                        i64 *__restrict__ adaptive_end)
 {
-    // speculative adaptive sub-steps (pysdm_b200_sort_by_key_if): the loop ended before this one
+    // speculative adaptive sub-steps (pysdm_b200_sort_by_key_if): the loop ended before this one.
+    // The sub-step this sort opens then does nothing either, and leaves the same verdict behind
+    // (adaptive_end: the word the fused sub-step this sort opens accumulates adaptive_sdm_end in,
+    // pysdm_b200_adaptive_presort)
+    if (threadIdx.x == 0 && adaptive_end != nullptr) adaptive_end[0] = 0;
     if (skip_if_zero != nullptr && *skip_if_zero == 0) return;
     __shared__ u32 hist[kRadixBins][kSmallSortWarps + 1];  // [digit][warp], padded
     __shared__ u32 warp_sums[kSmallSortWarps];
@@ -599,12 +605,18 @@ static size_t sort_by_key_ws_bytes(i64 n)
 
 PYSDM_EXPORT size_t pysdm_b200_sort_by_key_workspace_bytes(i64 n) { return sort_by_key_ws_bytes(n); }
 
+// fused.cu: the pre-pass on its own
+int pysdm_fused_prepass(const i64 *cell_start, i64 n_cell, double *norm_factor, double timestep,
+                        double dv, const i64 *rank_to_cell, const i64 *cell_idx, i64 *rank_info,
+                        i64 *adaptive_end, cudaStream_t st);
+
 static int sort_by_key_impl(i64 *idx, const double *attr, i64 n, void *ws, size_t ws_bytes,
-                            const i64 *skip_if_zero, cudaStream_t st)
+                            const i64 *skip_if_zero, i64 *adaptive_end, cudaStream_t st)
 {
     if (n <= 0) return 0;
     if (n == 1) {
         k_fill_i64<<<1, 32, 0, st>>>(idx, 0, 1);
+        if (adaptive_end != nullptr) cudaMemsetAsync(adaptive_end, 0, sizeof(i64), st);
         return LAUNCH_CHECK();
     }
     if (ws_bytes < sort_by_key_ws_bytes(n)) return (int)cudaErrorMemoryAllocation;
@@ -620,7 +632,7 @@ static int sort_by_key_impl(i64 *idx, const double *attr, i64 n, void *ws, size_
     u32 *scratch = (u32 *)w;
     if (n <= kSmallSortMax) {
         k_sort_by_key_small<<<1, kSmallSortThreads, 0, st>>>(attr, ka, va, kb, vb, idx, (int)n,
-                                                             skip_if_zero);
+                                                             skip_if_zero, adaptive_end);
         return LAUNCH_CHECK();
     }
     // (more keys than one CTA sorts: the skip word is not looked at, the sort always runs)
@@ -635,13 +647,14 @@ static int sort_by_key_impl(i64 *idx, const double *attr, i64 n, void *ws, size_
         va = vb;
         vb = tv;
     }
+    if (adaptive_end != nullptr) cudaMemsetAsync(adaptive_end, 0, sizeof(i64), st);
     return LAUNCH_CHECK();
 }
 
 PYSDM_EXPORT int pysdm_b200_sort_by_key(i64 *idx, const double *attr, i64 n, void *ws,
                                         size_t ws_bytes, void *stream)
 {
-    return sort_by_key_impl(idx, attr, n, ws, ws_bytes, nullptr, (cudaStream_t)stream);
+    return sort_by_key_impl(idx, attr, n, ws, ws_bytes, nullptr, nullptr, (cudaStream_t)stream);
 }
 
 // sort_by_key queued ahead of the read-back that decides whether it is needed (the adaptive
@@ -651,7 +664,29 @@ PYSDM_EXPORT int pysdm_b200_sort_by_key(i64 *idx, const double *attr, i64 n, voi
 PYSDM_EXPORT int pysdm_b200_sort_by_key_if(i64 *idx, const double *attr, i64 n, void *ws,
                                            size_t ws_bytes, const i64 *skip_if_zero, void *stream)
 {
-    return sort_by_key_impl(idx, attr, n, ws, ws_bytes, skip_if_zero, (cudaStream_t)stream);
+    return sort_by_key_impl(idx, attr, n, ws, ws_bytes, skip_if_zero, nullptr, (cudaStream_t)stream);
+}
+
+// Opens one sub-step of the adaptive loop (collision.py:181): the sort above, which also zeroes
+// the word the fused sub-step accumulates adaptive_sdm_end in; the per-rank part of that step's
+// pre-pass is followed inside the fused kernel (prepass_done), so ONE launch sits between two
+// launches of the fused step.  norm_factor != NULL: the per-cell factors of normalize() are
+// (re)computed first (they only depend on cell_start, timestep and dv).
+PYSDM_EXPORT int pysdm_b200_adaptive_presort(i64 *cell_idx, const double *dt_left, i64 n_cell,
+                                             void *ws, size_t ws_bytes, const i64 *skip_if_zero,
+                                             const i64 *cell_start, double *norm_factor,
+                                             double timestep, double dv, i64 *adaptive_end,
+                                             void *stream)
+{
+    if (n_cell <= 0 || !cell_idx || !dt_left || !adaptive_end) return (int)cudaErrorInvalidValue;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (norm_factor != nullptr) {
+        if (!cell_start) return (int)cudaErrorInvalidValue;
+        const int err = pysdm_fused_prepass(cell_start, n_cell, norm_factor, timestep, dv, nullptr,
+                                            nullptr, nullptr, nullptr, st);
+        if (err) return err;
+    }
+    return sort_by_key_impl(cell_idx, dt_left, n_cell, ws, ws_bytes, skip_if_zero, adaptive_end, st);
 }
 
 // ---------------------------------------------------------------------------------

@@ -283,6 +283,100 @@ PYSDM_EXPORT int pysdm_b200_calculate_displacement(
     return LAUNCH_CHECK();
 }
 
+// ---- one advection step of the particle positions in one launch -------------------------------
+// Displacement.__call__ without sedimentation (PySDM/dynamics/displacement.py:103-153) issues
+// calculate_displacement per dimension, `position += displacement`, `floor`, `cell_origin +=`,
+// `position -=` and `cell_origin %= grid` as seven passes over the [n_dims, n_sd] arrays.  Here
+// every super-droplet does all of it in registers, in the same order with the same operations:
+// the displacement of EVERY dimension is taken from the position before the update (as the
+// separate calls do), then per dimension the add, the floor, the integer add, the subtraction of
+// the converted floor and numpy's modulo.  `displacement` is still written (flag_precipitated
+// reads it afterwards).
+struct CourantField {
+    const double *data[3];
+    i64 s0[3], s1[3];  // row-major strides of component `dim` (it has one more entry along `dim`)
+    i64 grid[3];
+};
+
+template <int kDims>
+__global__ void k_displacement_step(bool implicit, double *__restrict__ displacement,
+                                    const CourantField f, i64 *__restrict__ cell_origin,
+                                    double *__restrict__ position_in_cell, i64 n_sd,
+                                    double n_substeps)
+{
+    const i64 d = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= n_sd) return;
+    i64 org[kDims];
+    double pos[kDims], disp[kDims];
+#pragma unroll
+    for (int k = 0; k < kDims; ++k) {
+        org[k] = cell_origin[(i64)k * n_sd + d];
+        pos[k] = position_in_cell[(i64)k * n_sd + d];
+    }
+#pragma unroll
+    for (int dim = 0; dim < kDims; ++dim) {  // k_displacement, for each component
+        i64 l, step;
+        if (kDims == 1) {
+            l = org[0];
+            step = 1;
+        } else if (kDims == 2) {
+            l = org[0] * f.s0[dim] + org[1];
+            step = dim == 0 ? f.s0[dim] : 1;
+        } else {
+            l = org[0] * f.s0[dim] + org[1] * f.s1[dim] + org[2];
+            step = dim == 0 ? f.s0[dim] : (dim == 1 ? f.s1[dim] : 1);
+        }
+        const double c_l = f.data[dim][l] / n_substeps, c_r = f.data[dim][l + step] / n_substeps;
+        double out = c_l * (1 - pos[dim]) + c_r * pos[dim];
+        if (implicit) out = out / (1 - c_r + c_l);
+        disp[dim] = out;
+    }
+#pragma unroll
+    for (int k = 0; k < kDims; ++k) {
+        const double moved = pos[k] + disp[k];        // update_position
+        const i64 fl = (i64)floor(moved);             // update_cell_origin: floor -> int64
+        i64 o = org[k] + fl;
+        const double p = moved - (double)fl;
+        const i64 g = f.grid[k];                      // boundary_condition: numpy's %
+        i64 r = o % g;
+        if (r != 0 && ((r < 0) != (g < 0))) r += g;
+        displacement[(i64)k * n_sd + d] = disp[k];
+        position_in_cell[(i64)k * n_sd + d] = p;
+        cell_origin[(i64)k * n_sd + d] = r;
+    }
+}
+
+PYSDM_EXPORT int pysdm_b200_displacement_step(
+    int n_dims, int implicit_in_space, double *displacement, const double *const *host_courant,
+    const i64 *host_courant_shapes, const i64 *host_grid, i64 *cell_origin,
+    double *position_in_cell, i64 n_sd, double n_substeps, void *stream)
+{
+    if (n_dims < 1 || n_dims > 3 || !host_courant || !host_courant_shapes || !host_grid)
+        return (int)cudaErrorInvalidValue;
+    if (n_sd <= 0) return 0;
+    CourantField f = {};
+    for (int dim = 0; dim < n_dims; ++dim) {
+        const i64 *shape = host_courant_shapes + (i64)dim * n_dims;  // shape of component `dim`
+        f.data[dim] = host_courant[dim];
+        if (f.data[dim] == nullptr || host_grid[dim] == 0) return (int)cudaErrorInvalidValue;
+        f.s0[dim] = n_dims == 2 ? shape[1] : (n_dims == 3 ? shape[1] * shape[2] : 0);
+        f.s1[dim] = n_dims == 3 ? shape[2] : 0;
+        f.grid[dim] = host_grid[dim];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool imp = implicit_in_space != 0;
+    if (n_dims == 1)
+        k_displacement_step<1><<<grid_for(n_sd), kThreads, 0, st>>>(
+            imp, displacement, f, cell_origin, position_in_cell, n_sd, n_substeps);
+    else if (n_dims == 2)
+        k_displacement_step<2><<<grid_for(n_sd), kThreads, 0, st>>>(
+            imp, displacement, f, cell_origin, position_in_cell, n_sd, n_substeps);
+    else
+        k_displacement_step<3><<<grid_for(n_sd), kThreads, 0, st>>>(
+            imp, displacement, f, cell_origin, position_in_cell, n_sd, n_substeps);
+    return LAUNCH_CHECK();
+}
+
 PYSDM_EXPORT int pysdm_b200_flag_precipitated(
     const i64 *cell_origin_z, const double *position_in_cell_z, const double *water_mass,
     const i64 *multiplicity, i64 *idx, i64 length, i64 idx_len, i64 *healthy,

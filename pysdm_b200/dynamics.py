@@ -81,6 +81,7 @@ def _make_classes():
             self._nf_slot = self._status = self._nf_facts = self._rank_info = None
             self._dependents = None  # derived attributes the fused step keeps current itself
             self._last_facts = None  # caretaker of the sort the last fused (sub-)step ran on
+            self._presort_nf = None  # the sort by cell norm_factor_temp was computed for (presort)
 
         def register(self, builder):
             super().register(builder)
@@ -143,8 +144,10 @@ def _make_classes():
             self.dt_left[:] = part.dt
             in_order = False
             while attrs.get_working_length() != 0:
-                attrs.cell_idx.sort_by_key(self.dt_left)
-                end = self.step(want_end=True)
+                prepass_done = self._presort()
+                if not prepass_done:
+                    attrs.cell_idx.sort_by_key(self.dt_left)
+                end = self.step(want_end=True, prepass_done=prepass_done)
                 in_order = end is not None
                 if end is None:  # not a fused sub-step, or super-droplets were removed
                     end = part.adaptive_sdm_end(self.dt_left)
@@ -164,6 +167,28 @@ def _make_classes():
             if self.enable_breakup:
                 self.rnd_opt_proc.reset()
                 self.rnd_opt_frag.reset()
+
+        def _presort(self):
+            """opens a sub-step with `cell_idx.sort_by_key(dt_left)` and the fused sub-step's
+            per-rank pre-pass in one launch, when the population is sorted by cell (nothing was
+            removed since) and the batched fused kernel is going to take the sub-step"""
+            part, attrs = self.particulator, self.particulator.attributes
+            if (not attrs._ParticleAttributes__sorted  # pylint: disable=protected-access
+                    or self._kernel_name() is None):
+                return False
+            keys = attrs._ParticleAttributes__extensive_keys  # pylint: disable=protected-access
+            facts = part.backend.sort_facts(attrs.cell_start.data)
+            if (facts is None or facts.max_cell is None or part.n_sd >= 2 ** 31
+                    or facts.max_cell > m.fused_max_cell_size()
+                    or ("signed water mass" not in keys and "water mass" not in keys)):
+                return False
+            sort_id = (facts, facts.n_sorts)
+            part.backend.adaptive_presort(
+                attrs.cell_idx, self.dt_left, cell_start=attrs.cell_start,
+                norm_factor=None if self._presort_nf == sort_id else self.norm_factor_temp,
+                timestep=part.dt, dv=part.mesh.dv, adaptive_end=self._words[1:2])
+            self._presort_nf = sort_id
+            return True
 
         def _kernel_name(self):
             """name of the fused kernel's instantiation for this configuration, or None when the
@@ -259,7 +284,7 @@ def _make_classes():
                 print(f"overflow ({n_overflow} pairs)\n\tfile: {__file__}"
                       "\n\tcontext:  collision_coalescence_breakup", file=sys.stderr)
 
-        def step(self, want_end=False):  # pylint: disable=arguments-differ
+        def step(self, want_end=False, prepass_done=False):  # pylint: disable=arguments-differ
             """one (sub-)step.  `want_end` (adaptive loop): returns adaptive_sdm_end's result
             when the fused launch computed it and it is still valid, else None"""
             plan = self._fused_plan()
@@ -313,7 +338,7 @@ def _make_classes():
                     "dt_left": self.dt_left.data, "stats_n_substep": self.stats_n_substep.data,
                     "stats_dt_min": self.stats_dt_min.data, "dt_min": self.dt_coal_range[0],
                     "dt_max": self.dt_coal_range[1], "rank_to_cell": facts.rank_to_cell,
-                    "rank_info": self._rank_info,
+                    "rank_info": self._rank_info, "prepass_done": prepass_done,
                     "adaptive_end": self._words[1:3] if want_end else None}
             else:
                 substeps = self._Collision__substeps  # pylint: disable=no-member

@@ -105,6 +105,20 @@ def shuffle_local(idx, u01, cell_start, length=None, max_cell=None):
                                        _stream()), "shuffle_local")
 
 
+def adaptive_presort(cell_idx, dt_left, *, cell_start, norm_factor, timestep, dv, adaptive_end,
+                     skip_if_zero=None):
+    """cell_idx.sort_by_key(dt_left) opening a fused adaptive sub-step, one launch
+    (pysdm_b200_adaptive_presort); the sub-step that follows passes prepass_done=True.
+    `norm_factor`: None when the per-cell factors are valid for the current cell_start"""
+    lib = _lib.load()
+    n = dt_left.numel()
+    ws = WS.dev("sort_by_key", lib.pysdm_b200_sort_by_key_workspace_bytes(n), cell_idx.device)
+    check(lib.pysdm_b200_adaptive_presort(
+        _pi(cell_idx), _pf(dt_left), n, _p(ws), ws.numel(), _pi(skip_if_zero), _pi(cell_start),
+        _pf(norm_factor), float(timestep), float(dv), _pi(adaptive_end), _stream()),
+        "adaptive_presort")
+
+
 SHUFFLE_STATIC_MAX_LENGTH = 262144  # PYSDM_B200_SHUFFLE_STATIC_MAX_LENGTH, include/pysdm_b200.h
 
 
@@ -329,6 +343,7 @@ def fused_collision_step(*, idx_in, idx_out, cell_start, cell_idx, cell_id_, mul
         args.rank_info = _pi(adaptive.get("rank_info"))
         args.adaptive_end = _pi(adaptive.get("adaptive_end"))
         args.length_dev = _pi(adaptive.get("length_dev"))
+        args.prepass_done = int(bool(adaptive.get("prepass_done", False)))
     if dependents is not None:  # see pysdm_b200_fused_args `dep_*`
         args.dep_volume = _pf(dependents.get("volume"))
         args.dep_radius = _pf(dependents.get("radius"))
@@ -565,6 +580,20 @@ def calculate_displacement(dim, displacement, courant, cell_origin, position_in_
         int(dim), n_dims, int(bool(implicit_in_space)), _pf(displacement), _pf(courant), shape,
         _pi(cell_origin), _pf(position_in_cell), n_sd, float(n_substeps), _stream()),
         "calculate_displacement")
+
+
+def displacement_step(displacement, courant, cell_origin, position_in_cell, grid, n_substeps=1,
+                      implicit_in_space=True):
+    """Displacement.__call__ without sedimentation in one launch (pysdm_b200_displacement_step):
+    `courant` = the components of the Courant field (device tensors), `grid` = host ints"""
+    n_dims, n_sd = displacement.shape
+    assert len(courant) == n_dims == len(grid)
+    pointers = (ctypes.c_void_p * n_dims)(*[_pf(c) for c in courant])
+    shapes = (ctypes.c_int64 * (n_dims * n_dims))(*[int(v) for c in courant for v in c.shape])
+    check(_lib.load().pysdm_b200_displacement_step(
+        n_dims, int(bool(implicit_in_space)), _pf(displacement), pointers, shapes,
+        (ctypes.c_int64 * n_dims)(*[int(g) for g in grid]), _pi(cell_origin),
+        _pf(position_in_cell), n_sd, float(n_substeps), _stream()), "displacement_step")
 
 
 def flag_precipitated(cell_origin, position_in_cell, water_mass, multiplicity, idx, length,

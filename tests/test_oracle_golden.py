@@ -199,7 +199,7 @@ def test_sort_by_key_and_cell_id(be, golden_methods, tag):
     np.testing.assert_array_equal(out, c["out"])
 
 
-@pytest.mark.parametrize("n", (1, 2, 33, 1000, 32768, 65536, 65537, 300000))
+@pytest.mark.parametrize("n", (1, 2, 33, 1000, 2048, 2049, 12345, 32768, 65536, 65537, 300000))
 def test_sort_by_key_sizes(be, n):
     """`argsort(kind="stable")[::-1]` (index_methods.py:46-48) at the sizes where the CUDA path
     switches algorithm (one-CTA sort up to 65536 keys, multi-kernel radix sort above), with
@@ -215,7 +215,7 @@ def test_sort_by_key_sizes(be, n):
 
 @pytest.mark.parametrize("shape", ("all_equal", "mostly_zero", "two_values", "low_bytes_differ",
                                    "one_nonzero", "all_distinct"))
-@pytest.mark.parametrize("n", (7, 4097, 32768))
+@pytest.mark.parametrize("n", (7, 4097, 20001, 32768))
 def test_sort_by_key_adaptive_shapes(be, n, shape):
     """the key sets the adaptive loop produces (collision.py:181, `dt_left` per cell): all equal
     before the first sub-step, mostly 0 afterwards -- the one-CTA sort treats the minimal key and

@@ -111,3 +111,49 @@ def test_flag_precipitated_and_out_of_column(be, g, tag):
     np.testing.assert_array_equal(idx, o["idx_out"])
     np.testing.assert_array_equal(healthy, o["healthy"])
     assert (o["idx_out"] == len(idx)).any()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_substeps", (1, 2))
+@pytest.mark.parametrize("n_dims", (1, 2, 3))
+@pytest.mark.parametrize("scheme", ("ImplicitInSpace", "ExplicitInSpace"))
+def test_displacement_step_one_launch(g, scheme, n_dims, n_substeps):
+    """pysdm_b200_displacement_step (Displacement.__call__ without sedimentation in one launch,
+    PySDM/dynamics/displacement.py:103-153) against the reference's displacement vectors and
+    the Storage operator chain applied to them in numpy, bit for bit; Courant numbers scaled up
+    so that positions leave their cells in both directions and wrap around the domain"""
+    import torch  # pylint: disable=import-outside-toplevel
+
+    from pysdm_b200 import methods as m  # pylint: disable=import-outside-toplevel
+
+    from . import device_adapter  # pylint: disable=import-outside-toplevel
+
+    c = case(g, f"displacement_{scheme}_{n_dims}d_{n_substeps}")
+    origin, pos = c["cell_origin"], c["position_in_cell"]
+    grid = [c["courant0"].shape[0] - 1] + list(c["courant0"].shape[1:])
+    for scale in (1.0, -3.7):
+        courant = [np.ascontiguousarray(c[f"courant{dim}"] * scale) for dim in range(n_dims)]
+        if scale == 1.0:
+            disp = c["displacement"]  # the reference's own output
+        else:  # the method-level kernel (pinned on the reference's vectors above)
+            disp = np.full_like(c["displacement"], np.nan)
+            for dim in range(n_dims):
+                device_adapter.calculate_displacement(
+                    dim, disp, courant[dim], origin, pos, int(c["n_substeps"]),
+                    implicit_in_space=scheme == "ImplicitInSpace")
+        moved = pos + disp
+        floor = np.floor(moved).astype(np.int64)
+        expected_origin = (origin + floor) % np.asarray(grid, dtype=np.int64)[:, None]
+        expected_pos = moved - floor
+        dev = torch.device("cuda:0")
+        d_disp = torch.full(disp.shape, float("nan"), dtype=torch.float64, device=dev)
+        d_origin, d_pos = torch.from_numpy(origin.copy()).to(dev), torch.from_numpy(pos.copy()).to(dev)
+        m.displacement_step(d_disp, [torch.from_numpy(x).to(dev) for x in courant], d_origin,
+                            d_pos, grid, n_substeps=int(c["n_substeps"]),
+                            implicit_in_space=scheme == "ImplicitInSpace")
+        assert_same_f64(d_disp.cpu().numpy(), disp, "displacement")
+        np.testing.assert_array_equal(d_origin.cpu().numpy(), expected_origin)
+        assert_same_f64(d_pos.cpu().numpy(), expected_pos, "position_in_cell")
+        if scale != 1.0:
+            assert (floor < 0).any() and (floor > 0).any()
+            assert ((origin + floor) < 0).any() or ((origin + floor) >= np.asarray(grid)[:, None]).any()

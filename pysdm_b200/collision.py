@@ -193,6 +193,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
         self.fused = fused
         self.n_fused_steps = 0
         self._epoch = 0
+        self._launch_cache = {}  # argument block of the fused launch (every array is allocated once)
         self._healthy_host = torch.ones(1, dtype=i64).pin_memory()
         self._words_host = torch.zeros(9, dtype=i64).pin_memory()
         # speculative stepping (step_async): gate word of the fused kernel, a ring of pinned
@@ -569,7 +570,7 @@ class DeviceCollision:  # pylint: disable=too-many-instance-attributes
             kernel_a=self.kernel.a, kernel_b=self.kernel.b, timestep=self.dt, dv=self.dv,
             rho_w=self.rho_w, substeps=1 if self.adaptive else self.substeps,
             nf_slot=self.nf_slot, refresh_nf=not self.nf_valid, gate=self.gate if gated else None,
-            epoch=self._epoch + 1, **kw)
+            epoch=self._epoch + 1, cache=self._launch_cache, **kw)
         m.check(err, "fused_collision_step")
         self.n_launches += 2 if self.adaptive else (1 if self.nf_valid else 3)
         self.nf_valid = not self.adaptive  # (cell_idx is re-sorted before every adaptive sub-step)

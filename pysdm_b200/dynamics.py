@@ -82,6 +82,7 @@ def _make_classes():
             self._dependents = None  # derived attributes the fused step keeps current itself
             self._last_facts = None  # caretaker of the sort the last fused (sub-)step ran on
             self._presort_nf = None  # the sort by cell norm_factor_temp was computed for (presort)
+            self._launch_cache = {}
 
         def register(self, builder):
             super().register(builder)
@@ -346,7 +347,20 @@ def _make_classes():
             ext = attrs.get_extensive_attribute_storage()
             sort_id = (facts, facts.n_sorts)
             RECORDER.flush_all()  # (this class drives the kernels directly: nothing may be pending)
+            # the argument block is kept between launches; this identifies everything in it that
+            # is not rewritten per launch (methods.fused_collision_step, `cache`)
+            static = [attrs.cell_start.data, attrs["cell id"].data, attrs["multiplicity"].data,
+                      ext.data, self.is_first_in_pair.indicator.data, self.gamma.data,
+                      self.norm_factor_temp.data, self.collision_rate.data,
+                      self.collision_rate_deficit.data, self.coalescence_rate.data, healthy.data]
+            for group in (kw, kw.get("adaptive", {}), kw.get("dependents", {})):
+                static.extend(v for k, v in group.items()
+                              if isinstance(v, torch.Tensor) and k not in ("u01", "rand",
+                                                                            "adaptive_end"))
+            cache_key = (name, kernel_a, kernel_b, part.dt, part.mesh.dv, substeps, mass_row,
+                         bool(self.enable_breakup), *(t.data_ptr() for t in static))
             err = m.fused_collision_step(
+                cache=self._launch_cache, cache_key=cache_key,
                 idx_in=idx.data, idx_out=facts.tmp_idx.data, cell_start=attrs.cell_start.data,
                 cell_idx=attrs.cell_idx.data, cell_id_=attrs["cell id"].data,
                 multiplicity=attrs["multiplicity"].data, attributes=ext.data,

@@ -59,7 +59,9 @@ _TORCH = {np.float64: torch.float64, np.int64: torch.int64, np.bool_: torch.bool
 
 
 def stream():
-    return torch.cuda.current_stream().cuda_stream
+    from .methods import _stream  # pylint: disable=import-outside-toplevel
+
+    return _stream()
 
 
 def ptr(tensor):

@@ -16,7 +16,12 @@ One JSON line on stdout (rank 0):
                         launch) against MEASURED_PEAKS.json; `traffic` = DRAM bytes of the
                         committed ncu capture, `achieved_dram` = traffic / launch time
   e2e                   the same step through the plug-in (Builder(backend=B200()) +
-                        Particulator.run(1)), HOST state in / out every step (pinned memory)
+                        Particulator.run(1)), HOST state in / out every step (pinned memory); the
+                        cells in 4 stripes, one Particulator and CUDA stream each, so that one
+                        stripe's upload overlaps another's read-back (measured: 4 stripes 6.9 ms,
+                        8: 8.2 ms, 16: 9.2 ms per step -- the host side of a stripe costs more
+                        than the shorter pipeline tail saves)
+  e2e_single_particulator   the same with one Particulator (no overlap of the two directions)
   e2e_striped           the same through HostCollisionStep (cells in stripes over 3 streams)
   cpu_baseline          the oracle port (and the reference's own Numba backend) on the host cores
   per_rank              elapsed time of every rank (N > 1)
@@ -69,6 +74,8 @@ def parse():
     ap.add_argument("--no-transport", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--e2e-stripes", type=int, default=4)
+    ap.add_argument("--e2e-plugin-stripes", type=int, default=4,
+                    help="Particulators (stripes of cells, one CUDA stream each) of the e2e leg")
     ap.add_argument("--config-steps", type=int, default=10)
     ap.add_argument("--transport-steps", type=int, default=20)
     return ap.parse_args()
@@ -411,11 +418,15 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
 
     # ---- e2e: host buffers in, host buffers out, every step (see DESIGN.md "measurement") ----
     if not args.no_e2e:
-        e2e = e2e_plugin(args, pop, rank, barrier, gather)
+        e2e = e2e_plugin(args, pop, rank, barrier, gather, stripes=args.e2e_plugin_stripes)
+        single = (e2e_plugin(args, pop, rank, barrier, gather, stripes=1)
+                  if e2e is not None and args.e2e_plugin_stripes > 1 else None)
         striped = e2e_striped(args, pop, rank, barrier, gather)
         if e2e is None:  # no PySDM on this box: the repo's own host-facing API is the e2e path
-            e2e, striped = striped, None
+            e2e, striped, single = striped, None, None
         line["e2e"] = e2e
+        if single is not None:
+            line["e2e_single_particulator"] = single
         if striped is not None:
             line["e2e_striped"] = striped
     if not args.no_transport:  # (N = 1: the same loop with one slab, the weak-scaling base line)
@@ -450,13 +461,16 @@ def gpu_arm(args):  # pylint: disable=too-many-locals,too-many-statements
         dist.destroy_process_group()
 
 
-def e2e_plugin(args, pop, rank, barrier, gather):
-    """the metric end to end through the reference-facing plug-in call: a `Particulator` built
-    by the unmodified `Builder(n_sd, backend=B200())` with the collision dynamic; every step
-    the super-droplet state (multiplicity, water mass) is uploaded from pinned host memory with
+def e2e_plugin(args, pop, rank, barrier, gather, stripes=1):
+    """the metric end to end through the reference-facing plug-in call: `Particulator`s built by
+    the unmodified `Builder(n_sd, backend=B200())` with the collision dynamic; every step the
+    super-droplet state (multiplicity, water mass) is uploaded from pinned host memory with
     `Storage.upload`, `particulator.run(1)` executes the step, and multiplicity, water mass and
     the per-cell coalescence counters are read back into pinned host memory with
-    `Storage.download`.  (`cell id` is not re-sent: it does not change in this workload.)"""
+    `Storage.download`.  (`cell id` is not re-sent: it does not change in this workload.)
+    `stripes` > 1: the cells are cut into that many contiguous stripes, one Particulator each
+    (cells do not interact), each driven under its own CUDA stream -- the upload of one stripe
+    then overlaps the read-back of another (PCIe is full duplex); same bytes, same work."""
     if not pysdm_paths():
         return None
     import torch  # pylint: disable=import-outside-toplevel
@@ -467,33 +481,51 @@ def e2e_plugin(args, pop, rank, barrier, gather):
 
     from pysdm_b200 import B200, FusedCoalescence  # pylint: disable=import-outside-toplevel
 
-    n_sd = len(pop["multiplicity"])
-    env = Box(dv=1.0, dt=1.0)
-    env.mesh = Mesh((pop["n_cell"],), size=(pop["n_cell"],), dv=1.0)
-    builder = Builder(n_sd=n_sd, backend=B200(Formulae(seed=1000 * (rank + 1))), environment=env)
-    builder.add_dynamic(FusedCoalescence(collision_kernel=Golovin(b=GOLOVIN_B), adaptive=False,
-                                         croupier="local"))
-    particulator = builder.build(products=(), attributes={
-        "multiplicity": pop["multiplicity"], "volume": pop["water_mass"] / RHO_W,
-        "cell id": pop["cell_id"]})
-    attrs, dyn = particulator.attributes, particulator.dynamics["Collision"]
-    mult, ext = attrs["multiplicity"], attrs.get_extensive_attribute_storage()
-    # the host model's state: two pinned buffer sets, a step reads one and writes the other
-    host = [(torch.from_numpy(pop["multiplicity"]).pin_memory(),
-             torch.from_numpy(pop["water_mass"]).reshape(1, -1).pin_memory()) for _ in range(2)]
-    out_rate = torch.empty(pop["n_cell"], dtype=torch.int64).pin_memory()
+    n_sd, n_cell = len(pop["multiplicity"]), pop["n_cell"]
+    sd_per_cell = n_sd // n_cell
+    parts = []
+    for s in range(stripes):
+        c0, c1 = n_cell * s // stripes, n_cell * (s + 1) // stripes
+        lo, hi = c0 * sd_per_cell, (n_sd if s == stripes - 1 else c1 * sd_per_cell)
+        env = Box(dv=1.0, dt=1.0)
+        env.mesh = Mesh((c1 - c0,), size=(c1 - c0,), dv=1.0)
+        builder = Builder(n_sd=hi - lo, backend=B200(Formulae(seed=1000 * (rank + 1) + s)),
+                          environment=env)
+        builder.add_dynamic(FusedCoalescence(collision_kernel=Golovin(b=GOLOVIN_B),
+                                             adaptive=False, croupier="local"))
+        particulator = builder.build(products=(), attributes={
+            "multiplicity": pop["multiplicity"][lo:hi],
+            "volume": pop["water_mass"][lo:hi] / RHO_W, "cell id": pop["cell_id"][lo:hi] - c0})
+        attrs, dyn = particulator.attributes, particulator.dynamics["Collision"]
+        # the host model's state: two pinned buffer sets, a step reads one and writes the other
+        host = [(torch.from_numpy(pop["multiplicity"][lo:hi].copy()).pin_memory(),
+                 torch.from_numpy(pop["water_mass"][lo:hi].copy()).reshape(1, -1).pin_memory())
+                for _ in range(2)]
+        parts.append({"particulator": particulator, "attrs": attrs, "dyn": dyn, "host": host,
+                      "mult": attrs["multiplicity"],
+                      "ext": attrs.get_extensive_attribute_storage(),
+                      "rate": torch.empty(c1 - c0, dtype=torch.int64).pin_memory(),
+                      "stream": torch.cuda.Stream() if stripes > 1 else torch.cuda.current_stream()})
+    main = torch.cuda.current_stream()
 
     def step():
-        (host_n, host_m), (out_n, out_m) = host
-        mult.upload(host_n)
-        ext.upload(host_m)
-        for key in ("multiplicity", *attrs.get_extensive_attribute_keys()):
-            attrs.mark_updated(key)
-        particulator.run(1)
-        mult.download(out_n)
-        ext.download(out_m)
-        dyn.coalescence_rate.download(out_rate)
-        host.reverse()  # the host model carries the state on
+        for p in parts:  # every stripe's upload is queued before anything waits
+            p["stream"].wait_stream(main)
+            with torch.cuda.stream(p["stream"]):
+                p["mult"].upload(p["host"][0][0])
+                p["ext"].upload(p["host"][0][1])
+        for p in parts:
+            with torch.cuda.stream(p["stream"]):
+                for key in ("multiplicity", *p["attrs"].get_extensive_attribute_keys()):
+                    p["attrs"].mark_updated(key)
+                p["particulator"].run(1)
+                p["mult"].download(p["host"][1][0], non_blocking=True)
+                p["ext"].download(p["host"][1][1], non_blocking=True)
+                p["dyn"].coalescence_rate.download(p["rate"], non_blocking=True)
+            p["host"].reverse()  # the host model carries the state on
+        for p in parts:  # the step's results are in host memory when step() returns
+            p["stream"].synchronize()
+            main.wait_stream(p["stream"])
 
     for _ in range(3):
         step()
@@ -506,24 +538,28 @@ def e2e_plugin(args, pop, rank, barrier, gather):
     barrier()
     per_rank = gather(beg.elapsed_time(end))
     ms = max(per_rank)
-    assert dyn.n_fused_steps >= args.e2e_steps and int(out_rate.sum()) > 0
+    assert all(p["dyn"].n_fused_steps >= args.e2e_steps and int(p["rate"].sum()) > 0 for p in parts)
     world = len(per_rank)
-    del particulator
+    del parts
     torch.cuda.empty_cache()
     return {"value": world * n_sd * args.e2e_steps / (ms * 1e-3), "unit": "SD-steps/s",
-            "h2d_bytes_per_step": n_sd * 16, "d2h_bytes_per_step": n_sd * 16 + pop["n_cell"] * 8,
+            "h2d_bytes_per_step": n_sd * 16, "d2h_bytes_per_step": n_sd * 16 + n_cell * 8,
             "steps": args.e2e_steps, "ms_per_step": ms / args.e2e_steps,
-            "per_rank_ms": per_rank,
-            "what": "plug-in: Builder(backend=B200()) + FusedCoalescence; per step Storage.upload "
-                    "of multiplicity and water mass from pinned host memory, "
-                    "Particulator.run(1), Storage.download of multiplicity, water mass and the "
-                    "coalescence counters into pinned host memory; PCIe-bound"}
+            "per_rank_ms": per_rank, "stripes": stripes,
+            "what": "plug-in: Builder(backend=B200()) + FusedCoalescence"
+                    + (f", {stripes} Particulators over {stripes} stripes of cells, one CUDA "
+                       "stream each (upload of one stripe overlaps the read-back of another)"
+                       if stripes > 1 else "")
+                    + "; per step Storage.upload of multiplicity and water mass from pinned host "
+                      "memory, Particulator.run(1), Storage.download of multiplicity, water mass "
+                      "and the coalescence counters into pinned host memory; PCIe-bound"}
 
 
 def e2e_striped(args, pop, rank, barrier, gather):
     """the same metric through the repo's own host-facing API
     (pysdm_b200.host_step.HostCollisionStep): every step uploads the super-droplet state
-    (multiplicity, water mass, cell id) from pinned host memory, runs sort-by-cell + the
+    (multiplicity, water mass; the cell ids once -- no droplet changes cell in this workload,
+    as in the plug-in leg) from pinned host memory, runs sort-by-cell + the
     collision step, and reads multiplicity, water mass and the coalescence counters back to
     pinned host memory; cells are cut into stripes so that upload, compute and download of
     different stripes overlap"""
@@ -536,14 +572,15 @@ def e2e_striped(args, pop, rank, barrier, gather):
         multiplicity=pop["multiplicity"], attributes=pop["water_mass"].reshape(1, -1),
         cell_id=pop["cell_id"], n_cell=pop["n_cell"], n_stripes=args.e2e_stripes,
         seed=1000 * (rank + 1), kernel=Golovin(GOLOVIN_B), dt=1.0, dv=1.0, fused=True)
+    host.step()  # (cell ids go up once: this workload moves no droplet between cells)
     for _ in range(3):
-        host.step()
+        host.step(cell_id_changed=False)
     launches0 = host.n_launches
     beg, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     beg.record()
     for _ in range(args.e2e_steps):
-        host.step()
+        host.step(cell_id_changed=False)
     end.record()
     barrier()
     per_rank = gather(beg.elapsed_time(end))
@@ -554,8 +591,9 @@ def e2e_striped(args, pop, rank, barrier, gather):
            "steps": args.e2e_steps, "ms_per_step": ms / args.e2e_steps,
            "gpu_launches": host.n_launches - launches0, "stripes": len(host.stripes),
            "per_rank_ms": per_rank,
-           "what": "HostCollisionStep: pinned host state -> H2D -> sort by cell + fused "
-                   "collision step -> D2H, cells in stripes over 3 streams"}
+           "what": "HostCollisionStep: pinned host state (multiplicity, water mass; cell ids "
+                   "unchanged, not re-sent) -> H2D -> sort by cell + fused collision step -> "
+                   "D2H, cells in stripes over 3 streams"}
     del host
     torch.cuda.empty_cache()
     return out

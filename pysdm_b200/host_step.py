@@ -75,9 +75,13 @@ class HostCollisionStep:  # pylint: disable=too-many-instance-attributes
         self.h2d_bytes = self.n_sd * 8 * (2 + self.attributes.shape[0])
         self.d2h_bytes = self.n_sd * 8 * (1 + self.attributes.shape[0]) + self.n_cell * 8
 
-    def step(self):
+    def step(self, cell_id_changed=True):
         """one model time step of the collision dynamic on the host arrays; returns when the
-        outputs are in `out_multiplicity`, `out_attributes`, `out_coalescence_rate`"""
+        outputs are in `out_multiplicity`, `out_attributes`, `out_coalescence_rate`.
+        `cell_id_changed=False`: the host model did not move any super-droplet to another cell
+        since the previous step (no transport between two collision steps): the cell ids on the
+        device are kept, a third of the upload"""
+        self.h2d_bytes = self.n_sd * 8 * ((2 if cell_id_changed else 1) + self.attributes.shape[0])
         # every upload is queued up front: the copy engine works through them while the host
         # drives sort + step of the stripes that have arrived
         for st in self.stripes:
@@ -85,13 +89,14 @@ class HostCollisionStep:  # pylint: disable=too-many-instance-attributes
             with torch.cuda.stream(self.s_in):
                 sim.multiplicity.copy_(self.multiplicity[sl], non_blocking=True)
                 sim.attributes.copy_(self.attributes[:, sl], non_blocking=True)
-                sim.cell_id.copy_(self.cell_id[sl], non_blocking=True)
+                if cell_id_changed:
+                    sim.cell_id.copy_(self.cell_id[sl], non_blocking=True)
                 st.arrived.record()
         for st in self.stripes:
             sim, sl = st.sim, slice(st.sb, st.se)
             with torch.cuda.stream(self.s_compute):
                 self.s_compute.wait_event(st.arrived)
-                if st.cb:
+                if st.cb and cell_id_changed:
                     sim.cell_id.sub_(st.cb)  # stripe-local cell numbers
                 sim.reset_permutation()
                 sim()

@@ -334,10 +334,11 @@ class Storage(StorageBase):
         if self.data._base is not None:  # pylint: disable=protected-access
             self.data = self.data.clone()
 
-    def download(self, target, reshape=False):
+    def download(self, target, reshape=False, non_blocking=False):
         self._peek()
         if isinstance(target, torch.Tensor):  # straight into (pinned) host memory
-            target.copy_(self.data.reshape(target.shape))
+            # non_blocking: the caller synchronises the stream before it reads `target`
+            target.copy_(self.data.reshape(target.shape), non_blocking=non_blocking)
             return
         host = self.data.cpu().numpy()
         if reshape:

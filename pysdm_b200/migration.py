@@ -64,7 +64,7 @@ class SlabMigrator:  # pylint: disable=too-many-instance-attributes
 
     def __init__(self, *, grid, rank, world, multiplicity, attributes, cell_origin,
                  position_in_cell, cell_id, idx, length, exchange_fn=exchange,
-                 neighbour_exchange_fn=None, capacity=None):
+                 neighbour_exchange_fn=None, capacity=None, neighbours_only=False):
         self.grid = tuple(int(n) for n in grid)
         self.rank, self.world = int(rank), int(world)
         self.rows = cell_range(self.grid[0], self.rank, self.world)
@@ -89,6 +89,7 @@ class SlabMigrator:  # pylint: disable=too-many-instance-attributes
         self.n_sent = self.n_received = 0
         # neighbour exchange: records per direction, buffers, device counters (csrc/migration.cu)
         self.neighbour_exchange_fn = neighbour_exchange_fn or neighbour_exchange
+        self.neighbours_only = bool(neighbours_only)
         # (a few per cent of the population per direction; exceeding it is reported, not silent)
         self.cap = int(capacity or os.environ.get("PYSDM_MIG_CAP") or max(4096, self.n_cap // 64))
         self.send = torch.zeros((2, self.cap + 1, self.n_words), dtype=torch.int64, device=dev)
@@ -130,8 +131,15 @@ class SlabMigrator:  # pylint: disable=too-many-instance-attributes
         cell_id is valid (slab-local) for all of them, and the population is NOT sorted by cell."""
         self.split()
         self.neighbour_exchange_fn(self.send, self.recv, self.rank, self.world)
-        if self.merge(all_reduce_far=self.world > 1):  # some rank saw a far mover: all ranks
-            self.migrate_general()                     # run the general path on what is left
+        if self.neighbours_only:
+            # the caller vouches that no droplet moves farther than one slab per exchange
+            # (Courant numbers below one with slabs at least one row thick): no agreement
+            # between the ranks is needed, so no collective couples them all in every step
+            if self.merge(all_reduce_far=False):
+                raise RuntimeError(f"rank {self.rank}: a droplet moved beyond a neighbour slab "
+                                   "although the migrator was built with neighbours_only=True")
+        elif self.merge(all_reduce_far=self.world > 1):  # some rank saw a far mover: all ranks
+            self.migrate_general()                       # run the general path on what is left
         return self.length
 
     def migrate_general(self):

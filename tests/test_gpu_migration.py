@@ -89,3 +89,20 @@ def test_migration_nccl_two_gpus():
         capture_output=True, text=True, timeout=600, check=False)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-4000:]
     assert "migration ok rank 0" in out.stdout and "migration ok rank 1" in out.stdout
+
+
+def test_migration_neighbours_only_world_1():
+    """`neighbours_only=True` (no agreement between the ranks on far movers): migrate() is the
+    neighbour exchange alone; a droplet beyond a neighbour slab raises instead of being moved"""
+    from .migration_common import Shard, global_population  # pylint: disable=import-outside-toplevel
+
+    pop = global_population()
+    shard = Shard(pop, 0, 1)
+    shard.migrator.neighbours_only = True
+    shard.displace()
+    shard.migrator.migrate()
+    assert shard.check(pop) == pop["multiplicity"].size and shard.migrator.n_general == 0
+    # a far mover, as merge() reports it (status bit 1 of the device counters)
+    shard.migrator.merge = lambda all_reduce_far=False: True
+    with pytest.raises(RuntimeError, match="neighbours_only"):
+        shard.migrator.migrate()

@@ -79,8 +79,10 @@ class HostCollisionStep:  # pylint: disable=too-many-instance-attributes
         """one model time step of the collision dynamic on the host arrays; returns when the
         outputs are in `out_multiplicity`, `out_attributes`, `out_coalescence_rate`.
         `cell_id_changed=False`: the host model did not move any super-droplet to another cell
-        since the previous step (no transport between two collision steps): the cell ids on the
-        device are kept, a third of the upload"""
+        since the previous step (no transport between two collision steps) and did not revive
+        removed ones: the cell ids on the device are kept -- a third of the upload -- and so is
+        the permutation with its sort by cell, as `Particulator.run` keeps them from step to
+        step (no identity permutation, no re-sort, no scan for zero multiplicities)"""
         self.h2d_bytes = self.n_sd * 8 * ((2 if cell_id_changed else 1) + self.attributes.shape[0])
         # every upload is queued up front: the copy engine works through them while the host
         # drives sort + step of the stripes that have arrived
@@ -96,9 +98,10 @@ class HostCollisionStep:  # pylint: disable=too-many-instance-attributes
             sim, sl = st.sim, slice(st.sb, st.se)
             with torch.cuda.stream(self.s_compute):
                 self.s_compute.wait_event(st.arrived)
-                if st.cb and cell_id_changed:
-                    sim.cell_id.sub_(st.cb)  # stripe-local cell numbers
-                sim.reset_permutation()
+                if cell_id_changed:
+                    if st.cb:
+                        sim.cell_id.sub_(st.cb)  # stripe-local cell numbers
+                    sim.reset_permutation()
                 sim()
                 st.computed.record()
             with torch.cuda.stream(self.s_out):

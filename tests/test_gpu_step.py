@@ -277,6 +277,42 @@ def test_host_step_stripes_equal_separate_runs():
     assert rate.sum() > 0 and host.h2d_bytes == mult.size * 8 * 4
 
 
+def test_host_step_keeps_permutation_when_cells_are_unchanged():
+    """HostCollisionStep.step(cell_id_changed=False): cell ids are not re-sent and the
+    permutation with its sort by cell is carried from step to step, as a DeviceCollision that
+    is simply called again carries it"""
+    from pysdm_b200.host_step import HostCollisionStep  # pylint: disable=import-outside-toplevel
+    from pysdm_b200.sharding import shard_population  # pylint: disable=import-outside-toplevel
+
+    pop = ragged_population(seed=12, n_cell=200, mean=60, n_attr=1)
+    order = np.argsort(pop["cell_id"], kind="stable")
+    mult, cid = pop["multiplicity"][order], pop["cell_id"][order]
+    attrs = pop["water_mass"][order].reshape(1, -1)
+    kw = dict(dt=1.0, dv=2e-7)
+    n_stripes = 2
+    host = HostCollisionStep(multiplicity=mult, attributes=attrs, cell_id=cid, n_cell=200,
+                             n_stripes=n_stripes, seed=5, kernel=device_kernel(b=GOLOVIN_B), **kw)
+    refs = []
+    for s in range(n_stripes):
+        n_s, a_s, c_s, n_cell_s, mine = shard_population(mult, attrs, cid, 200, s, n_stripes)
+        refs.append((device_sim(multiplicity=n_s, water_mass=a_s[0], cell_id=c_s, n_cell=n_cell_s,
+                                seed=5 + s, kernel=device_kernel(b=GOLOVIN_B), **kw), mine))
+    removed = 0
+    for step in range(5):
+        host.step(cell_id_changed=step == 0)
+        assert host.h2d_bytes == mult.size * 8 * (3 if step == 0 else 2)
+        for sim, mine in refs:
+            sim()
+            np.testing.assert_array_equal(host.out_multiplicity.numpy()[mine],
+                                          sim.host("multiplicity"), f"step {step}")
+            assert_same_f64(host.out_attributes.numpy()[:, mine], sim.host("attributes"),
+                            f"step {step} attributes")
+        removed = sum(sim.n_sd - sim.length for sim, _ in refs)
+        host.multiplicity.copy_(host.out_multiplicity)
+        host.attributes.copy_(host.out_attributes)
+    assert removed > 0, "super-droplets were expected to be removed along the way"
+
+
 @pytest.mark.parametrize("adaptive", (False, True))
 def test_full_size_fused_equals_oracle(adaptive):
     """BASELINE.json's headline size -- 2^24 super-droplets in 2^17 cells of 128, the bench.py
